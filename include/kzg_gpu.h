@@ -1,0 +1,129 @@
+/* kzg_gpu.h — C ABI of the B200 (sm_100a) hot path for uncommitted6453/kzg-commitments.
+ *
+ * This is the ONLY interface the host side (the kzg.h drop-in in src/, the Python mirror in
+ * kzg-commitments_b200/, tests and bench.py) links against.  Plain pointers and sizes, no C++ or
+ * torch types.  Every function returns 0 on success and a negative kzg_gpu_status otherwise; nothing
+ * throws or aborts.  There is NO CPU fallback behind any entry point: without a CUDA device
+ * kzg_gpu_ctx_create fails with KZG_GPU_ERR_CUDA.
+ *
+ * Reference interfaces replaced (paths relative to the reference repository):
+ *   kzg_gpu_msm_g1 / _batch        trusted_setup::polyeval_G1     src/trusted_setup.cpp:149-174
+ *                                  (called by create_commit :137-142, create_proof :227, verify_proof :246)
+ *   kzg_gpu_msm_g2                 trusted_setup::polyeval_G2     src/trusted_setup.cpp:176-201
+ *   kzg_gpu_poly_quotient          ZZ_pX q = (P - I) / Z          src/trusted_setup.cpp:218-225
+ *   kzg_gpu_poly_eval_range        evaluate_polynomial_points     src/util.cpp:186-211
+ *   kzg_gpu_prove                  create_proof body              src/trusted_setup.cpp:214-228
+ *   kzg_gpu_setup_powers           trusted_setup(int) + generate_elements_range
+ *                                                                 src/trusted_setup.cpp:21-74, 123-135
+ *   kzg_gpu_srs_load               the _G1/_G2 vectors a trusted_setup holds (src/kzg.h:183-185),
+ *                                  in the octet-body layout of export_setup (src/trusted_setup.cpp:256-287)
+ *
+ * Byte formats (identical to what the reference itself produces, so no translation layer is needed):
+ *   scalar / coefficient  SB = CURVE_ORDER_BYTES little-endian bytes = BytesFromZZ(buf, rep(c), SB)
+ *                         (src/util.cpp:31-43).  Values >= r are reduced mod r like PAIR_G1mul does.
+ *   G1 point              x | y, each M = MODBYTES_CURVE big-endian canonical bytes = the body of
+ *                         ECP_toOctet(.., compress=false) after the 0x04 tag (miracl-core/cpp/ecp.cpp:445-491).
+ *   G2 point              x.b | x.a | y.b | y.a (imaginary part first; ecp2.cpp:209-215, fp2.cpp:83-87).
+ *   infinity              all-zero coordinates (what ECP_toOctet leaves for the point at infinity),
+ *                         additionally flagged through the is_inf outputs.
+ *   M / SB:  BN158 20/20, BN254 32/32, BLS12381 48/32.
+ */
+#ifndef KZG_GPU_H
+#define KZG_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct kzg_gpu_ctx kzg_gpu_ctx; /* opaque: owns device memory, stream, tables */
+
+enum kzg_gpu_curve { KZG_GPU_BN158 = 0, KZG_GPU_BN254 = 1, KZG_GPU_BLS12381 = 2 };
+
+enum kzg_gpu_status {
+  KZG_GPU_OK = 0,
+  KZG_GPU_ERR_ARG = -1,    /* bad argument (null pointer, range outside the loaded SRS, unknown curve) */
+  KZG_GPU_ERR_CUDA = -2,   /* CUDA runtime error (no device, launch failure); see kzg_gpu_last_error */
+  KZG_GPU_ERR_MEMORY = -3, /* device or pinned allocation failed */
+  KZG_GPU_ERR_STATE = -4   /* call order (e.g. MSM before an SRS is resident) */
+};
+
+const char* kzg_gpu_strerror(int status);
+/* last CUDA error text recorded on this context (empty string if none) */
+const char* kzg_gpu_last_error(const kzg_gpu_ctx* ctx);
+
+/* sizes for a curve: M (MODBYTES_CURVE) and SB (CURVE_ORDER_BYTES); < 0 for an unknown curve */
+int kzg_gpu_modbytes(int curve);
+int kzg_gpu_scalar_bytes(int curve);
+
+/* One context per (curve, device).  `device` is a CUDA ordinal. */
+int kzg_gpu_ctx_create(kzg_gpu_ctx** out, int curve, int device);
+void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
+
+/* Tunables (mostly for bench/tests): "window_bits" (0 = auto), "precompute" (0/1: build the
+ * per-SRS window table at srs_load), "task_chunk", "reduce_chunk".  Takes effect at the next srs_load / MSM. */
+int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value);
+
+/* Make an SRS resident.  g1: n * 2M bytes.  g2: n * 4M bytes or NULL (G1-only use). */
+int kzg_gpu_srs_load(kzg_gpu_ctx* ctx, uint64_t n, const uint8_t* g1, const uint8_t* g2);
+
+/* [s^i]G1 (n * 2M bytes) and [s^i]G2 (n * 4M bytes) for i < n from the secret s (SB little-endian
+ * bytes); either output may be NULL.  The generated SRS is left resident (as after srs_load). */
+int kzg_gpu_setup_powers(kzg_gpu_ctx* ctx, const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out);
+
+/* out = sum_{i<count} scalars[i] * G1[base_offset + i]   (host buffers) */
+int kzg_gpu_msm_g1(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t base_offset,
+                   uint8_t* out_xy /* 2M */, int* is_inf);
+int kzg_gpu_msm_g2(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t base_offset,
+                   uint8_t* out_xy /* 4M */, int* is_inf);
+/* `batch` independent MSMs over the same bases G1[0..count): scalars is batch*count*SB bytes,
+ * out is batch*2M bytes, is_inf is batch ints. */
+int kzg_gpu_msm_g1_batch(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t batch,
+                         uint8_t* out_xy, int* is_inf);
+
+/* Device-resident variants: `d_scalars` is a DEVICE pointer (same byte layout).  _launch only
+ * enqueues on the context stream (result stays on device); _fetch waits and copies the results of
+ * the most recent launch.  Used for kernel-only timing and for pipelines that produce scalars on device. */
+int kzg_gpu_msm_g1_launch(kzg_gpu_ctx* ctx, const void* d_scalars, uint64_t count, uint64_t batch, uint64_t base_offset);
+int kzg_gpu_msm_fetch(kzg_gpu_ctx* ctx, uint8_t* out_xy, int* is_inf);
+/* projective (XYZZ, Montgomery limbs) result of the most recent single launch, for the multi-GPU
+ * point-range split: each rank fetches 4*L words, ranks exchange them (NCCL all-gather / host) and
+ * one rank folds them with kzg_gpu_g1_sum_partials. */
+int kzg_gpu_msm_fetch_partial(kzg_gpu_ctx* ctx, uint32_t* xyzz_words, size_t* n_words);
+int kzg_gpu_g1_sum_partials(kzg_gpu_ctx* ctx, const uint32_t* xyzz_words, uint64_t n_partials,
+                            uint8_t* out_xy /* 2M */, int* is_inf);
+
+/* q = P div prod_{j<k} (x - (first_root + j)): coeffs n*SB bytes in, (n-k)*SB bytes out (k < n). */
+int kzg_gpu_poly_quotient(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k,
+                          uint8_t* q_out);
+/* y_j = P(first_root + j), j < k: k*SB bytes out. */
+int kzg_gpu_poly_eval_range(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k,
+                            uint8_t* y_out);
+/* create_proof: quotient and G1 MSM chained on device (the quotient never visits the host).
+ * k >= n gives the zero quotient, i.e. the point at infinity (benchmark "Proofs: 4096" row). */
+int kzg_gpu_prove(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k,
+                  uint8_t* out_xy /* 2M */, int* is_inf);
+
+/* The context's CUDA stream (cudaStream_t) so a caller can time with events on it. */
+void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx);
+/* kernels launched by this context since creation (bench.py's gpu_launches) */
+uint64_t kzg_gpu_launch_count(const kzg_gpu_ctx* ctx);
+
+/* Integer-pipe microbenchmarks used for the roofline denominator:
+ * kind 0: independent mad.lo.cc/madc.hi.cc chains (-> IMAD.WIDE.U32.X), returns 32x32 products/s
+ * kind 1: independent plain 32-bit IMAD (mad.lo.u32), returns instructions/s
+ * kind 2: Fp Montgomery products/s of the context's curve (register-resident operands)
+ * kind 3: Fr Montgomery products/s */
+int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops_per_second);
+
+/* Device self-test: field, Fp2 and group-law identities on random inputs, compared on device against
+ * independent formulations (e.g. (a+b)^2 = a^2+2ab+b^2, P+Q-Q = P, [r]G = inf).  Returns the number of
+ * failed checks in *failures. */
+int kzg_gpu_selftest(kzg_gpu_ctx* ctx, int* failures);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KZG_GPU_H */

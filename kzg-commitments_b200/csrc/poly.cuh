@@ -1,0 +1,155 @@
+// Fr polynomial kernels for create_proof (src/trusted_setup.cpp:214-228).
+//
+//   poly_quotient    q = P div Z,  Z = prod_{j<k} (x - (first_root + j))
+//                    == the reference's  (P - I) / Z  (src/trusted_setup.cpp:225 -> NTL div,
+//                    ntl/src/ZZ_pX.cpp:3953): I = P mod Z has degree < k, so the quotient is the same.
+//                    Computed WITHOUT I, Z or the evaluations: k synthetic divisions by a linear
+//                    factor, each a first-order linear recurrence  q[i] = p[i+1] + a*q[i+1]
+//                    evaluated as a suffix scan inside one CTA.
+//   poly_eval_range  y_j = P(first_root + j)   (evaluate_polynomial_points, src/util.cpp:186-211)
+//
+// Coefficients travel as little-endian SCALAR_BYTES records (BytesFromZZ layout, src/util.cpp:31-43)
+// and are held in Montgomery form on device.  BN curves have 2-adicity 2, so nothing here uses an NTT.
+#pragma once
+#include "field.cuh"
+
+namespace kzgb200 {
+
+template <class C>
+KZG_D Field<typename C::FrP> fr_load(const uint8_t* src, uint64_t idx) {
+  using Fr = Field<typename C::FrP>;
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(src + idx * C::SCALAR_BYTES);
+  Fr k;
+#pragma unroll
+  for (int i = 0; i < Fr::L; i++) k.v[i] = (i < C::SCALAR_WORDS) ? w[i] : 0u;
+  // the Montgomery product reduces any input below 2^(32L) when multiplied by R^2 < r
+  return Fr::to_mont(k);
+}
+template <class C>
+KZG_D void fr_store(uint8_t* dst, uint64_t idx, const Field<typename C::FrP>& m) {
+  using Fr = Field<typename C::FrP>;
+  Fr k = Fr::from_mont(m);
+  uint32_t* w = reinterpret_cast<uint32_t*>(dst + idx * C::SCALAR_BYTES);
+#pragma unroll
+  for (int i = 0; i < C::SCALAR_WORDS; i++) w[i] = k.v[i];
+}
+
+// (first_root + j) mod r in Montgomery form; first_root may be negative
+template <class C>
+KZG_D Field<typename C::FrP> fr_from_i64(long long x) {
+  using Fr = Field<typename C::FrP>;
+  Fr k = Fr::zero();
+  unsigned long long mag = x < 0 ? (unsigned long long)(-(x + 1)) + 1ull : (unsigned long long)x;
+  k.v[0] = (uint32_t)mag;
+  k.v[1] = (uint32_t)(mag >> 32);
+  Fr m = Fr::to_mont(k);
+  return x < 0 ? Fr::neg(m) : m;
+}
+
+template <class Fr>
+KZG_D Fr fr_pow_u32(Fr base, uint32_t e) {
+  Fr r = Fr::one();
+  while (e) {
+    if (e & 1) r = Fr::mul(r, base);
+    base = Fr::sqr(base);
+    e >>= 1;
+  }
+  return r;
+}
+
+// bytes -> Montgomery (grid-stride)
+template <class C>
+__global__ void fr_from_bytes(uint64_t n, const uint8_t* __restrict__ in, Field<typename C::FrP>* __restrict__ out) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    out[i] = fr_load<C>(in, i);
+}
+template <class C>
+__global__ void fr_to_bytes(uint64_t n, const Field<typename C::FrP>* __restrict__ in, uint8_t* __restrict__ out) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    fr_store<C>(out, i, in[i]);
+}
+
+// ---------------------------------------------------------------- quotient by k consecutive linear factors
+// Single CTA.  buf0 holds P (n coefficients, Montgomery); buf1 is scratch of the same size.
+// After round j the current polynomial has n-1-j coefficients.  The result (n-k coefficients) ends
+// in buf0 if k is even, buf1 if k is odd.
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+poly_quotient_rounds(uint64_t n, long long first_root, uint64_t k, Field<typename C::FrP>* buf0,
+                     Field<typename C::FrP>* buf1) {
+  using Fr = Field<typename C::FrP>;
+  __shared__ Fr s_val[THREADS];
+  __shared__ Fr s_mul[THREADS];
+  const int tid = threadIdx.x;
+  Fr* src = buf0;
+  Fr* dst = buf1;
+  uint64_t m = n;  // current coefficient count
+  for (uint64_t round = 0; round < k; round++) {
+    const Fr a = fr_from_i64<C>(first_root + (long long)round);
+    // thread t owns source indices [lo, hi), segments ordered by index; carry flows from high to low
+    const uint64_t seg = (m + THREADS - 1) / THREADS;
+    const uint64_t lo = min(seg * (uint64_t)tid, m), hi = min(lo + seg, m);
+    // h = sum_{j in [lo,hi)} src[j] * a^(j-lo)
+    Fr h = Fr::zero();
+    for (uint64_t j = hi; j > lo; j--) h = Fr::add(Fr::mul(h, a), src[j - 1]);
+    // value carried INTO this segment from above:  c_t = sum_{j >= hi} src[j] * a^(j-hi)
+    // suffix scan over threads of the affine maps  c -> h_t + a^len_t * c
+    s_val[tid] = h;
+    s_mul[tid] = fr_pow_u32<Fr>(a, (uint32_t)(hi - lo));
+    __syncthreads();
+    for (int d = 1; d < THREADS; d <<= 1) {
+      Fr v = s_val[tid], mu = s_mul[tid];
+      Fr v2 = Fr::zero(), mu2 = Fr::one();
+      const bool has = tid + d < THREADS;
+      if (has) { v2 = s_val[tid + d]; mu2 = s_mul[tid + d]; }
+      __syncthreads();
+      if (has) {
+        // compose: first apply the upper block (tid+d ...), then this one
+        s_val[tid] = Fr::add(v, Fr::mul(mu, v2));
+        s_mul[tid] = Fr::mul(mu, mu2);
+      }
+      __syncthreads();
+    }
+    // s_val[t] = sum_{j >= lo_t} src[j] a^(j-lo_t); the carry into segment t is s_val[t+1]
+    Fr c = (tid + 1 < THREADS) ? s_val[tid + 1] : Fr::zero();
+    // q[i] = src[i+1] + a*q[i+1]; with c = q-value "at index hi-1":  q[hi-1] = c? no:
+    // define r[j] = sum_{j' >= j} src[j'] a^(j'-j)  (so c = r[hi]); then q[j-1] = r[j] for j >= 1.
+    for (uint64_t j = hi; j > lo; j--) {
+      // here c == r[j]
+      if (j >= 1 && j - 1 < m - 1) dst[j - 1] = c;          // q[j-1] = r[j]   (q has m-1 coefficients)
+      c = Fr::add(Fr::mul(c, a), src[j - 1]);               // r[j-1]
+    }
+    __syncthreads();
+    Fr* t = src; src = dst; dst = t;
+    m -= 1;
+  }
+}
+
+// ---------------------------------------------------------------- evaluation at consecutive points
+// One CTA per point: thread t Horner-evaluates its slice, scales by x^lo, CTA tree-sums.
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+poly_eval_range_kernel(uint64_t n, long long first_root, uint64_t k, const Field<typename C::FrP>* __restrict__ coeffs,
+                       Field<typename C::FrP>* __restrict__ ys) {
+  using Fr = Field<typename C::FrP>;
+  __shared__ Fr s_val[THREADS];
+  const int tid = threadIdx.x;
+  for (uint64_t pt = blockIdx.x; pt < k; pt += gridDim.x) {
+    const Fr x = fr_from_i64<C>(first_root + (long long)pt);
+    const uint64_t seg = (n + THREADS - 1) / THREADS;
+    const uint64_t lo = min(seg * (uint64_t)tid, n), hi = min(lo + seg, n);
+    Fr h = Fr::zero();
+    for (uint64_t j = hi; j > lo; j--) h = Fr::add(Fr::mul(h, x), coeffs[j - 1]);
+    if (hi > lo) h = Fr::mul(h, fr_pow_u32<Fr>(x, (uint32_t)lo));
+    s_val[tid] = h;
+    __syncthreads();
+    for (int s = THREADS / 2; s > 0; s >>= 1) {
+      if (tid < s) s_val[tid] = Fr::add(s_val[tid], s_val[tid + s]);
+      __syncthreads();
+    }
+    if (tid == 0) ys[pt] = s_val[0];
+    __syncthreads();
+  }
+}
+
+}  // namespace kzgb200

@@ -1,0 +1,139 @@
+// Powers-of-tau batch: [s^i]G1 and [s^i]G2 for i < n, replacing
+//   trusted_setup::trusted_setup(int)            src/trusted_setup.cpp:21-74
+//   trusted_setup::generate_elements_range       src/trusted_setup.cpp:123-135
+// (n independent NTL power() calls, then one PAIR_G1mul and one PAIR_G2mul per index spread over
+// std::threads).  Here: s^i by chunked running products, then a fixed-base comb — a table
+// T[w][d-1] = d * 2^(8w) * G (d = 1..128, affine) built once per context, 8-bit signed digits,
+// one mixed add per window, one inversion per output point.
+// Also: the per-SRS precomputed window table used by the MSM (msm.cuh).
+#pragma once
+#include "msm.cuh"
+#include "poly.cuh"
+
+namespace kzgb200 {
+
+constexpr int FB_C = 8;                       // fixed-base window bits
+constexpr int FB_HALF = 1 << (FB_C - 1);      // 128 table entries per window
+
+template <class C>
+constexpr int fb_windows() { return (C::SCALAR_BITS + 1 + FB_C - 1) / FB_C; }
+
+// powers[i] = s^i (canonical little-endian words, NOT Montgomery), i < n.
+// Thread t produces indices [t*S, (t+1)*S): s^(t*S) by square-and-multiply, then S-1 products.
+template <class C>
+__global__ void setup_powers(uint64_t n, const uint8_t* __restrict__ s_bytes, int per_thread,
+                             uint32_t* __restrict__ powers /* n * FrP::L words */) {
+  using Fr = Field<typename C::FrP>;
+  const uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  const uint64_t lo = t * (uint64_t)per_thread;
+  if (lo >= n) return;
+  const uint64_t hi = min(lo + (uint64_t)per_thread, n);
+  uint32_t k[Fr::L];
+  load_scalar<C>(s_bytes, 0, k);
+  Fr s;
+#pragma unroll
+  for (int i = 0; i < Fr::L; i++) s.v[i] = k[i];
+  s = Fr::to_mont(s);
+  // s^lo, lo < 2^64
+  Fr cur = Fr::one(), base = s;
+  for (uint64_t e = lo; e; e >>= 1) {
+    if (e & 1) cur = Fr::mul(cur, base);
+    base = Fr::sqr(base);
+  }
+  for (uint64_t i = lo; i < hi; i++) {
+    Fr c = Fr::from_mont(cur);
+#pragma unroll
+    for (int j = 0; j < Fr::L; j++) powers[i * Fr::L + j] = c.v[j];
+    cur = Fr::mul(cur, s);
+  }
+}
+
+// table[w * 128 + (d-1)] = d * 2^(8w) * G    (one thread per entry; context-creation time only)
+template <class C, class F>
+__global__ void fixed_base_table(Affine<F> gen, Affine<F>* __restrict__ table) {
+  constexpr int W = fb_windows<C>();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= W * FB_HALF) return;
+  const int w = t / FB_HALF, d = (t % FB_HALF) + 1;
+  constexpr int KW = (W * FB_C + FB_C + 31) / 32 + 1;
+  uint32_t k[KW];
+  for (int i = 0; i < KW; i++) k[i] = 0;
+  const int pos = w * FB_C;
+  k[pos >> 5] |= (uint32_t)d << (pos & 31);
+  if ((pos & 31) + 8 > 32) k[(pos >> 5) + 1] |= (uint32_t)d >> (32 - (pos & 31));
+  XYZZ<F> r = scalar_mul_bits<F>(gen, k, pos + FB_C);
+  table[t] = r.to_affine();
+}
+
+// out[i] = powers[i] * G  as affine bytes (reference octet body layout) and Montgomery affine points
+template <class C, class F>
+__global__ void __launch_bounds__(128)
+fixed_base_mul(uint64_t n, const uint32_t* __restrict__ powers, const Affine<F>* __restrict__ table,
+               Affine<F>* __restrict__ out_points, uint8_t* __restrict__ out_bytes, int modbytes) {
+  using Fr = Field<typename C::FrP>;
+  constexpr int W = fb_windows<C>();
+  const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t k[Fr::L];
+#pragma unroll
+  for (int j = 0; j < Fr::L; j++) k[j] = powers[i * Fr::L + j];
+  XYZZ<F> acc = XYZZ<F>::inf();
+  uint32_t carry = 0;
+  for (int w = 0; w < W; w++) {
+    uint32_t raw = scalar_bits<Fr::L>(k, w * FB_C, FB_C) + carry;
+    int d;
+    if (raw > (uint32_t)FB_HALF) { d = (int)raw - (1 << FB_C); carry = 1; }
+    else { d = (int)raw; carry = 0; }
+    if (d != 0) {
+      const int mag = d < 0 ? -d : d;
+      const Affine<F> p = table[w * FB_HALF + (mag - 1)];
+      acc.madd(p, d < 0);
+    }
+  }
+  const Affine<F> a = acc.to_affine();
+  if (out_points) out_points[i] = a;
+  if (out_bytes) {
+    const int nbytes = CoordCount<F>::value * modbytes;
+    if (acc.is_inf()) { for (int j = 0; j < nbytes; j++) out_bytes[i * nbytes + j] = 0; }
+    else affine_to_bytes(a, out_bytes + i * nbytes, modbytes);
+  }
+}
+
+// MSM window table:  table[w * stride + i] = 2^(c*w) * base[i],  w < W  (row 0 = the SRS itself).
+// One thread per point; the W projective values are normalised with ONE inversion (Montgomery's
+// trick over the thread's own W values), which is why the scratch lives in local memory.
+template <class F, int MAXW>
+__global__ void __launch_bounds__(128)
+msm_precompute_table(uint64_t n, uint64_t stride, int c, int W, const Affine<F>* __restrict__ base,
+                     Affine<F>* __restrict__ table) {
+  const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const Affine<F> p0 = base[i];
+  table[i] = p0;
+  if (p0.is_inf()) {
+    for (int w = 1; w < W; w++) table[(uint64_t)w * stride + i] = p0;
+    return;
+  }
+  XYZZ<F> cur = XYZZ<F>::from_affine(p0);
+  XYZZ<F> pts[MAXW];
+  F pref[MAXW];  // pref[w] = prod_{v<=w} ZZZ_v
+  F run = F::one();
+  for (int w = 1; w < W; w++) {
+    for (int k = 0; k < c; k++) cur.dbl();
+    pts[w] = cur;                      // infinity only for points outside the prime-order subgroup
+    run = F::mul(run, cur.is_inf() ? F::one() : cur.ZZZ);
+    pref[w] = run;
+  }
+  F inv = F::inv(run);
+  for (int w = W - 1; w >= 1; w--) {
+    const F before = (w > 1) ? pref[w - 1] : F::one();
+    if (pts[w].is_inf()) { table[(uint64_t)w * stride + i] = Affine<F>::inf(); continue; }
+    const F i3 = F::mul(inv, before);          // 1 / ZZZ_w
+    inv = F::mul(inv, pts[w].ZZZ);
+    const F i1 = F::mul(pts[w].ZZ, i3);
+    const F i2 = F::sqr(i1);
+    table[(uint64_t)w * stride + i] = Affine<F>{F::mul(pts[w].X, i2), F::mul(pts[w].Y, i3)};
+  }
+}
+
+}  // namespace kzgb200
