@@ -1,178 +1,114 @@
-// C ABI (include/kzg_gpu.h) over the CUDA kernels: one templated context per curve parameter set
-// (config/curve_{BN158,BN254,BLS12381}/kzg_config.h in the reference select the same three sets at
-// compile time; here all three live in one library and are selected at kzg_gpu_ctx_create).
-#include "../../include/kzg_gpu.h"
-
-#include <cuda_runtime.h>
-
-#include <algorithm>
-#include <cstdio>
-#include <cstring>
-#include <mutex>
-#include <new>
-#include <string>
-#include <vector>
-
-#include "curve_constants.cuh"
-#include "diag.cuh"
-#include "msm.cuh"
-#include "poly.cuh"
-#include "setup.cuh"
+// extern "C" entry points of include/kzg_gpu.h; the per-curve contexts live in curve_*.cu.
+#include "ctx.cuh"
 
 using namespace kzgb200;
 
-namespace {
+// ---------------------------------------------------------------------------------------------
+extern "C" {
 
-struct DevBuf {
-  void* p = nullptr;
-  size_t cap = 0;
-  cudaError_t ensure(size_t bytes) {
-    if (bytes <= cap) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-    size_t want = bytes + bytes / 8 + 256;
-    cudaError_t e = cudaMalloc(&p, want);
-    if (e == cudaSuccess) cap = want;
-    return e;
+const char* kzg_gpu_strerror(int status) {
+  switch (status) {
+    case KZG_GPU_OK: return "ok";
+    case KZG_GPU_ERR_ARG: return "invalid argument";
+    case KZG_GPU_ERR_CUDA: return "CUDA error";
+    case KZG_GPU_ERR_MEMORY: return "out of device memory";
+    case KZG_GPU_ERR_STATE: return "invalid call order (no SRS resident?)";
+    default: return "unknown status";
   }
-  void release() {
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-  }
-  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
-};
-
-int ilog2(uint64_t v) {
-  int r = 0;
-  while (v >>= 1) r++;
-  return r;
 }
 
-}  // namespace
+const char* kzg_gpu_last_error(const kzg_gpu_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
 
-// ---------------------------------------------------------------------------------------------
-struct kzg_gpu_ctx {
-  int curve = -1;
-  int device = 0;
-  cudaStream_t stream = nullptr;
-  std::string last_error;
-  uint64_t launches = 0;
-  std::mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
-  // options
-  int opt_window_bits = 0, opt_precompute = 0, opt_task_chunk = 0, opt_reduce_chunk = 0;
-
-  virtual ~kzg_gpu_ctx() {}
-  virtual int srs_load(uint64_t n, const uint8_t* g1, const uint8_t* g2) = 0;
-  virtual int setup_powers(const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) = 0;
-  virtual int msm(int group, const uint8_t* scalars, bool scalars_on_device, uint64_t count, uint64_t batch,
-                  uint64_t base_offset, uint8_t* out, int* is_inf, bool fetch) = 0;
-  virtual int fetch(uint8_t* out, int* is_inf) = 0;
-  virtual int fetch_partial(uint32_t* words, size_t* n_words) = 0;
-  virtual int sum_partials(const uint32_t* words, uint64_t n, uint8_t* out, int* is_inf) = 0;
-  virtual int poly_quotient(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) = 0;
-  virtual int poly_eval(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* y_out) = 0;
-  virtual int prove(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out, int* is_inf) = 0;
-  virtual int microbench(int kind, double* ops) = 0;
-  virtual int selftest(int* failures) = 0;
-
-  int cuda_fail(cudaError_t e, const char* where) {
-    char buf[256];
-    snprintf(buf, sizeof buf, "%s: %s", where, cudaGetErrorString(e));
-    last_error = buf;
-    return e == cudaErrorMemoryAllocation ? KZG_GPU_ERR_MEMORY : KZG_GPU_ERR_CUDA;
+int kzg_gpu_modbytes(int curve) {
+  switch (curve) {
+    case KZG_GPU_BN158: return Curve_BN158::MODBYTES;
+    case KZG_GPU_BN254: return Curve_BN254::MODBYTES;
+    case KZG_GPU_BLS12381: return Curve_BLS12381::MODBYTES;
+    default: return KZG_GPU_ERR_ARG;
   }
-};
-
-#define CK(call)                                                  \
-  do {                                                            \
-    cudaError_t e__ = (call);                                     \
-    if (e__ != cudaSuccess) return cuda_fail(e__, #call);         \
-  } while (0)
-#define LAUNCHED()                                                \
-  do {                                                            \
-    launches++;                                                   \
-    cudaError_t e__ = cudaGetLastError();                         \
-    if (e__ != cudaSuccess) return cuda_fail(e__, "kernel launch"); \
-  } while (0)
-
-template <class C>
-struct Ctx final : kzg_gpu_ctx {
-  using Fp = Field<typename C::FpP>;
-  using Fp2 = Field2<typename C::FpP>;
-  using Fr = Field<typename C::FrP>;
-  static constexpr int M = C::MODBYTES;
-  static constexpr int SB = C::SCALAR_BYTES;
-  static constexpr int MAXW = 40;
-
-  // resident SRS
-  uint64_t srs_n = 0;
-  bool have_g2 = false;
-  DevBuf g1, g2;             // Affine<Fp>[n], Affine<Fp2>[n]
-  DevBuf g1_table;           // precomputed window table (row 0 unused: g1 itself is row 0's content)
-  int table_c = 0, table_W = 0;
-  // fixed-base tables of the generators
-  DevBuf fb1, fb2;
-  bool fb_ready = false;
-  // scratch
-  DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, chunk_out, group_out, out_bytes,
-      out_inf, out_xyzz, poly0, poly1, qbytes, powers;
-  // description of the most recent launch, for fetch()
-  uint64_t last_batch = 0;
-  int last_group = 1;
-
-  ~Ctx() override {
-    cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first, &cursor,
-                      &sorted, &partial, &chunk_out, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
-                      &qbytes, &powers})
-      b->release();
-    if (stream) cudaStreamDestroy(stream);
+}
+int kzg_gpu_scalar_bytes(int curve) {
+  switch (curve) {
+    case KZG_GPU_BN158: return Curve_BN158::SCALAR_BYTES;
+    case KZG_GPU_BN254: return Curve_BN254::SCALAR_BYTES;
+    case KZG_GPU_BLS12381: return Curve_BLS12381::SCALAR_BYTES;
+    default: return KZG_GPU_ERR_ARG;
   }
+}
 
-  int init() {
-    CK(cudaSetDevice(device));
-    CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    return KZG_GPU_OK;
+int kzg_gpu_ctx_create(kzg_gpu_ctx** out, int curve, int device) {
+  if (!out) return KZG_GPU_ERR_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return KZG_GPU_ERR_CUDA;  // no CPU fallback
+  if (device < 0 || device >= ndev) return KZG_GPU_ERR_ARG;
+  kzg_gpu_ctx* c = nullptr;
+  int rc = KZG_GPU_OK;
+  switch (curve) {
+    case KZG_GPU_BN158: c = kzg_gpu_make_ctx_bn158(device, &rc); break;
+    case KZG_GPU_BN254: c = kzg_gpu_make_ctx_bn254(device, &rc); break;
+    case KZG_GPU_BLS12381: c = kzg_gpu_make_ctx_bls12381(device, &rc); break;
+    default: return KZG_GPU_ERR_ARG;
   }
+  if (!c) return rc ? rc : KZG_GPU_ERR_MEMORY;
+  c->curve = curve;
+  *out = c;
+  return KZG_GPU_OK;
+}
 
-  // ------------------------------------------------------------------ SRS
-  int build_table() {
-    g1_table.release();
-    table_c = table_W = 0;
-    if (!opt_precompute || srs_n == 0) return KZG_GPU_OK;
-    int c = opt_window_bits ? opt_window_bits : std::min(16, std::max(8, ilog2(srs_n) - 2));
-    int W = (C::SCALAR_BITS + 1 + c - 1) / c;
-    if (W > MAXW) return KZG_GPU_ERR_ARG;
-    CK(g1_table.ensure((size_t)W * srs_n * sizeof(Affine<Fp>)));
-    msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
-        srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>());
-    LAUNCHED();
-    CK(cudaStreamSynchronize(stream));
-    table_c = c;
-    table_W = W;
-    return KZG_GPU_OK;
-  }
+void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx) { delete ctx; }
 
-  int srs_load(uint64_t n, const uint8_t* h_g1, const uint8_t* h_g2) override {
-    if (!h_g1 || n == 0) return KZG_GPU_ERR_ARG;
-    CK(cudaSetDevice(device));
-    CK(g1.ensure(n * sizeof(Affine<Fp>)));
-    CK(stage.ensure(n * (size_t)(4 * M)));
-    CK(cudaMemcpyAsync(stage.p, h_g1, n * (size_t)(2 * M), cudaMemcpyHostToDevice, stream));
-    points_from_bytes<Fp><<<(unsigned)((n + 127) / 128), 128, 0, stream>>>(n, stage.as<uint8_t>(), M, g1.as<Affine<Fp>>());
-    LAUNCHED();
-    CK(cudaStreamSynchronize(stream));
-    have_g2 = false;
-    if (h_g2) {
-      CK(g2.ensure(n * sizeof(Affine<Fp2>)));
-      CK(cudaMemcpyAsync(stage.p, h_g2, n * (size_t)(4 * M), cudaMemcpyHostToDevice, stream));
-      points_from_bytes<Fp2><<<(unsigned)((n + 127) / 128), 128, 0, stream>>>(n, stage.as<uint8_t>(), M, g2.as<Affine<Fp2>>());
-      LAUNCHED();
-      CK(cudaStreamSynchronize(stream));
-      have_g2 = true;
-    }
-    srs_n = n;
-    return build_table();
-  }
+int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value) {
+  if (!ctx || !name) return KZG_GPU_ERR_ARG;
+  std::string n(name);
+  if (n == "window_bits") { if (value != 0 && (value < 2 || value > 22)) return KZG_GPU_ERR_ARG; ctx->opt_window_bits = (int)value; }
+  else if (n == "precompute") ctx->opt_precompute = value ? 1 : 0;
+  else if (n == "task_chunk") { if (value < 0 || value > (1 << 20)) return KZG_GPU_ERR_ARG; ctx->opt_task_chunk = (int)value; }
+  else if (n == "reduce_chunk") { if (value < 0 || (value & (value - 1))) return KZG_GPU_ERR_ARG; ctx->opt_reduce_chunk = (int)value; }
+  else return KZG_GPU_ERR_ARG;
+  return KZG_GPU_OK;
+}
+
+int kzg_gpu_srs_load(kzg_gpu_ctx* ctx, uint64_t n, const uint8_t* g1, const uint8_t* g2) {
+  if (!ctx) return KZG_GPU_ERR_ARG;
+  std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+  return ctx->srs_load(n, g1, g2);
+}
+int kzg_gpu_setup_powers(kzg_gpu_ctx* ctx, const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) {
+  return ctx ? ctx->setup_powers(s_le, n, g1_out, g2_out) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_msm_g1(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t base_offset, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->msm(1, scalars, false, count, 1, base_offset, out_xy, is_inf, true) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_msm_g2(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t base_offset, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->msm(2, scalars, false, count, 1, base_offset, out_xy, is_inf, true) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_msm_g1_batch(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t batch, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->msm(1, scalars, false, count, batch, 0, out_xy, is_inf, true) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_msm_g1_launch(kzg_gpu_ctx* ctx, const void* d_scalars, uint64_t count, uint64_t batch, uint64_t base_offset) {
+  return ctx ? ctx->msm(1, static_cast<const uint8_t*>(d_scalars), true, count, batch, base_offset, nullptr, nullptr, false)
+             : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_msm_fetch(kzg_gpu_ctx* ctx, uint8_t* out_xy, int* is_inf) { return ctx ? ctx->fetch(out_xy, is_inf) : KZG_GPU_ERR_ARG; }
+int kzg_gpu_msm_fetch_partial(kzg_gpu_ctx* ctx, uint32_t* words, size_t* n_words) {
+  return ctx ? ctx->fetch_partial(words, n_words) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_g1_sum_partials(kzg_gpu_ctx* ctx, const uint32_t* words, uint64_t n, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->sum_partials(words, n, out_xy, is_inf) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_poly_quotient(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) {
+  return ctx ? ctx->poly_quotient(coeffs, n, first_root, k, q_out) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_poly_eval_range(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* y_out) {
+  return ctx ? ctx->poly_eval(coeffs, n, first_root, k, y_out) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_prove(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->prove(coeffs, n, first_root, k, out_xy, is_inf) : KZG_GPU_ERR_ARG;
+}
+void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+uint64_t kzg_gpu_launch_count(const kzg_gpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops) { return ctx ? ctx->microbench(kind, ops) : KZG_GPU_ERR_ARG; }
+int kzg_gpu_selftest(kzg_gpu_ctx* ctx, int* failures) { return ctx ? ctx->selftest(failures) : KZG_GPU_ERR_ARG; }
+
+}  // extern "C"

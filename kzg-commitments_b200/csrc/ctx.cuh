@@ -1,0 +1,558 @@
+// Host-side context behind the C ABI (include/kzg_gpu.h): one templated context per curve parameter
+// set.  config/curve_{BN158,BN254,BLS12381}/kzg_config.h in the reference select the same three sets
+// at compile time; here each set is one translation unit (curve_*.cu, compiled in parallel) and all
+// three live in one library, selected at kzg_gpu_ctx_create.
+#pragma once
+#include "../../include/kzg_gpu.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "curve_constants.cuh"
+#include "diag.cuh"
+#include "msm.cuh"
+#include "poly.cuh"
+#include "setup.cuh"
+
+using namespace kzgb200;
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+int ilog2(uint64_t v) {
+  int r = 0;
+  while (v >>= 1) r++;
+  return r;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+struct kzg_gpu_ctx {
+  int curve = -1;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string last_error;
+  uint64_t launches = 0;
+  std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
+  // options
+  int opt_window_bits = 0, opt_precompute = 0, opt_task_chunk = 0, opt_reduce_chunk = 0;
+
+  virtual ~kzg_gpu_ctx() {}
+  virtual int srs_load(uint64_t n, const uint8_t* g1, const uint8_t* g2) = 0;
+  virtual int setup_powers(const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) = 0;
+  virtual int msm(int group, const uint8_t* scalars, bool scalars_on_device, uint64_t count, uint64_t batch,
+                  uint64_t base_offset, uint8_t* out, int* is_inf, bool fetch) = 0;
+  virtual int fetch(uint8_t* out, int* is_inf) = 0;
+  virtual int fetch_partial(uint32_t* words, size_t* n_words) = 0;
+  virtual int sum_partials(const uint32_t* words, uint64_t n, uint8_t* out, int* is_inf) = 0;
+  virtual int poly_quotient(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) = 0;
+  virtual int poly_eval(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* y_out) = 0;
+  virtual int prove(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out, int* is_inf) = 0;
+  virtual int microbench(int kind, double* ops) = 0;
+  virtual int selftest(int* failures) = 0;
+
+  int cuda_fail(cudaError_t e, const char* where) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "%s: %s", where, cudaGetErrorString(e));
+    last_error = buf;
+    return e == cudaErrorMemoryAllocation ? KZG_GPU_ERR_MEMORY : KZG_GPU_ERR_CUDA;
+  }
+};
+
+#define CK(call)                                                  \
+  do {                                                            \
+    cudaError_t e__ = (call);                                     \
+    if (e__ != cudaSuccess) return cuda_fail(e__, #call);         \
+  } while (0)
+#define LAUNCHED()                                                \
+  do {                                                            \
+    launches++;                                                   \
+    cudaError_t e__ = cudaGetLastError();                         \
+    if (e__ != cudaSuccess) return cuda_fail(e__, "kernel launch"); \
+  } while (0)
+
+template <class C>
+struct Ctx final : kzg_gpu_ctx {
+  using Fp = Field<typename C::FpP>;
+  using Fp2 = Field2<typename C::FpP>;
+  using Fr = Field<typename C::FrP>;
+  static constexpr int M = C::MODBYTES;
+  static constexpr int SB = C::SCALAR_BYTES;
+  static constexpr int MAXW = 40;
+
+  // resident SRS
+  uint64_t srs_n = 0;
+  bool have_g2 = false;
+  DevBuf g1, g2;             // Affine<Fp>[n], Affine<Fp2>[n]
+  DevBuf g1_table;           // precomputed window table (row 0 unused: g1 itself is row 0's content)
+  int table_c = 0, table_W = 0;
+  // fixed-base tables of the generators
+  DevBuf fb1, fb2;
+  bool fb_ready = false;
+  // scratch
+  DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, chunk_out, group_out, out_bytes,
+      out_inf, out_xyzz, poly0, poly1, qbytes, powers;
+  // description of the most recent launch, for fetch()
+  uint64_t last_batch = 0;
+  int last_group = 1;
+
+  ~Ctx() override {
+    cudaSetDevice(device);
+    for (DevBuf* b : {&g1, &g2, &g1_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first, &cursor,
+                      &sorted, &partial, &chunk_out, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
+                      &qbytes, &powers})
+      b->release();
+    if (stream) cudaStreamDestroy(stream);
+  }
+
+  int init() {
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    return KZG_GPU_OK;
+  }
+
+  // ------------------------------------------------------------------ SRS
+  int build_table() {
+    g1_table.release();
+    table_c = table_W = 0;
+    if (!opt_precompute || srs_n == 0) return KZG_GPU_OK;
+    int c = opt_window_bits ? opt_window_bits : std::min(16, std::max(8, ilog2(srs_n) - 2));
+    int W = (C::SCALAR_BITS + 1 + c - 1) / c;
+    if (W > MAXW) return KZG_GPU_ERR_ARG;
+    CK(g1_table.ensure((size_t)W * srs_n * sizeof(Affine<Fp>)));
+    msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
+        srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>());
+    LAUNCHED();
+    CK(cudaStreamSynchronize(stream));
+    table_c = c;
+    table_W = W;
+    return KZG_GPU_OK;
+  }
+
+  int srs_load(uint64_t n, const uint8_t* h_g1, const uint8_t* h_g2) override {
+    if (!h_g1 || n == 0) return KZG_GPU_ERR_ARG;
+    CK(cudaSetDevice(device));
+    CK(g1.ensure(n * sizeof(Affine<Fp>)));
+    CK(stage.ensure(n * (size_t)(4 * M)));
+    CK(cudaMemcpyAsync(stage.p, h_g1, n * (size_t)(2 * M), cudaMemcpyHostToDevice, stream));
+    points_from_bytes<Fp><<<(unsigned)((n + 127) / 128), 128, 0, stream>>>(n, stage.as<uint8_t>(), M, g1.as<Affine<Fp>>());
+    LAUNCHED();
+    CK(cudaStreamSynchronize(stream));
+    have_g2 = false;
+    if (h_g2) {
+      CK(g2.ensure(n * sizeof(Affine<Fp2>)));
+      CK(cudaMemcpyAsync(stage.p, h_g2, n * (size_t)(4 * M), cudaMemcpyHostToDevice, stream));
+      points_from_bytes<Fp2><<<(unsigned)((n + 127) / 128), 128, 0, stream>>>(n, stage.as<uint8_t>(), M, g2.as<Affine<Fp2>>());
+      LAUNCHED();
+      CK(cudaStreamSynchronize(stream));
+      have_g2 = true;
+    }
+    srs_n = n;
+    return build_table();
+  }
+
+  // ------------------------------------------------------------------ MSM
+  // Enqueue one Pippenger pass for `batch` MSMs of `count` scalars (device-resident bytes).
+  // Leaves affine bytes + flags in out_bytes/out_inf and the projective result of each MSM in out_xyzz.
+  template <class F>
+  int enqueue_msm(const Affine<F>* bases, const Affine<F>* table, const uint8_t* d_scalars, uint64_t count,
+                  uint64_t batch, uint64_t base_offset) {
+    MsmShape sh;
+    const bool precomp = table != nullptr;
+    sh.c = precomp ? table_c : (opt_window_bits ? opt_window_bits : std::min(16, std::max(8, ilog2(count) - 4)));
+    if (count < 32 && !precomp && !opt_window_bits) sh.c = 4;
+    sh.W = (C::SCALAR_BITS + 1 + sh.c - 1) / sh.c;
+    sh.nb = 1 << (sh.c - 1);
+    sh.precomp = precomp ? 1 : 0;
+    sh.groups_per_msm = precomp ? 1 : sh.W;
+    sh.n = count;
+    sh.batch = batch;
+    sh.table_stride = srs_n;
+    sh.base_offset = base_offset;
+    sh.chunk = opt_task_chunk ? opt_task_chunk : 64;
+    const uint64_t records = count * batch * (uint64_t)sh.W;
+    if (records >= (1ull << 31) || (precomp && (uint64_t)sh.W * srs_n >= (1ull << 31))) return KZG_GPU_ERR_ARG;
+    const uint64_t nbuckets = sh.total_buckets();
+    const uint64_t max_tasks = records / sh.chunk + nbuckets + 1;
+    int bpc = opt_reduce_chunk ? opt_reduce_chunk : 16;
+    bpc = std::min(bpc, sh.nb);
+    const int cpg = sh.nb / bpc;
+    const uint64_t groups = sh.total_groups();
+
+    CK(digits.ensure(records * 4));
+    CK(sorted.ensure(records * 4));
+    CK(counts.ensure((nbuckets + 1) * 4));
+    CK(starts.ensure((nbuckets + 1) * 4));
+    CK(task_first.ensure((nbuckets + 1) * 4));
+    CK(cursor.ensure((nbuckets + 1) * 4));
+    CK(partial.ensure(max_tasks * sizeof(XYZZ<F>)));
+    CK(chunk_out.ensure(groups * cpg * sizeof(XYZZ<F>)));
+    CK(group_out.ensure(groups * sizeof(XYZZ<F>)));
+    CK(out_bytes.ensure(batch * (size_t)(4 * M)));
+    CK(out_inf.ensure(batch * sizeof(int)));
+    CK(out_xyzz.ensure(batch * sizeof(XYZZ<F>)));
+
+    const int sms = 148;
+    CK(cudaMemsetAsync(counts.p, 0, (nbuckets + 1) * 4, stream));
+    {
+      const uint64_t total = count * batch;
+      unsigned grid = (unsigned)std::min<uint64_t>((total + 255) / 256, (uint64_t)sms * 16);
+      msm_digits<C><<<grid, 256, 0, stream>>>(sh, d_scalars, digits.as<int32_t>(), counts.as<uint32_t>());
+      LAUNCHED();
+    }
+    msm_scan<<<1, 1024, 0, stream>>>(nbuckets, sh.chunk, counts.as<uint32_t>(), starts.as<uint32_t>(),
+                                     task_first.as<uint32_t>(), cursor.as<uint32_t>());
+    LAUNCHED();
+    {
+      unsigned grid = (unsigned)std::min<uint64_t>((records + 255) / 256, (uint64_t)sms * 32);
+      msm_scatter<<<grid, 256, 0, stream>>>(sh, digits.as<int32_t>(), starts.as<uint32_t>(), cursor.as<uint32_t>(),
+                                            sorted.as<uint32_t>());
+      LAUNCHED();
+    }
+    {
+      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 64);
+      msm_accumulate<F><<<grid, 128, 0, stream>>>(nbuckets, task_first.as<uint32_t>(), starts.as<uint32_t>(),
+                                                  sorted.as<uint32_t>(), precomp ? table : bases,
+                                                  partial.as<XYZZ<F>>());
+      LAUNCHED();
+    }
+    {
+      const uint64_t total = groups * cpg;
+      unsigned grid = (unsigned)std::min<uint64_t>((total + 127) / 128, (uint64_t)sms * 64);
+      msm_reduce_chunks<F><<<grid, 128, 0, stream>>>(groups, sh.nb, bpc, task_first.as<uint32_t>(),
+                                                     partial.as<XYZZ<F>>(), chunk_out.as<XYZZ<F>>());
+      LAUNCHED();
+    }
+    {
+      constexpr int RT = 64;  // 64 * sizeof(XYZZ) = 12-24 KiB of shared memory
+      msm_reduce_groups<F, RT><<<(unsigned)groups, RT, RT * sizeof(XYZZ<F>), stream>>>(
+          cpg, chunk_out.as<XYZZ<F>>(), group_out.as<XYZZ<F>>());
+      LAUNCHED();
+    }
+    msm_finish<F><<<(unsigned)((batch + 31) / 32), 32, 0, stream>>>(
+        batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
+        out_xyzz.as<XYZZ<F>>());
+    LAUNCHED();
+    last_batch = batch;
+    return KZG_GPU_OK;
+  }
+
+  // largest number of MSMs of `count` scalars that one pass may take
+  uint64_t max_batch_per_pass(uint64_t count, int W) const {
+    const uint64_t rec_budget = 1ull << 27;  // records per pass (digits + sorted = 1 GiB)
+    uint64_t b = rec_budget / std::max<uint64_t>(1, count * (uint64_t)W);
+    return std::max<uint64_t>(1, b);
+  }
+
+  int msm(int group, const uint8_t* scalars, bool on_device, uint64_t count, uint64_t batch, uint64_t base_offset,
+          uint8_t* out, int* is_inf, bool do_fetch) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (srs_n == 0) return KZG_GPU_ERR_STATE;
+    if (group == 2 && !have_g2) return KZG_GPU_ERR_STATE;
+    if ((count && !scalars) || batch == 0) return KZG_GPU_ERR_ARG;
+    if (base_offset + count > srs_n || base_offset + count < count) return KZG_GPU_ERR_ARG;
+    last_group = group;
+    const int nco = group == 2 ? 4 : 2;
+    if (count == 0) {  // empty sum = infinity (polyeval_G1 on the zero polynomial, src/trusted_setup.cpp:150-154)
+      if (do_fetch) {
+        if (out) memset(out, 0, batch * (size_t)(nco * M));
+        if (is_inf) for (uint64_t b = 0; b < batch; b++) is_inf[b] = 1;
+      }
+      last_batch = 0;
+      return KZG_GPU_OK;
+    }
+    const bool use_table = group == 1 && g1_table.p != nullptr;
+    const int Wguess = use_table ? table_W : (C::SCALAR_BITS + 8) / 8;
+    const uint64_t per_pass = do_fetch ? max_batch_per_pass(count, Wguess) : batch;
+    for (uint64_t b0 = 0; b0 < batch; b0 += per_pass) {
+      const uint64_t nb = std::min(per_pass, batch - b0);
+      const uint8_t* d_scal;
+      if (on_device) {
+        d_scal = scalars + b0 * count * SB;
+      } else {
+        CK(scal.ensure(nb * count * (size_t)SB));
+        CK(cudaMemcpyAsync(scal.p, scalars + b0 * count * SB, nb * count * (size_t)SB, cudaMemcpyHostToDevice, stream));
+        d_scal = scal.as<uint8_t>();
+      }
+      int rc;
+      if (group == 1)
+        rc = enqueue_msm<Fp>(g1.as<Affine<Fp>>(), use_table ? g1_table.as<Affine<Fp>>() : nullptr, d_scal, count, nb,
+                             base_offset);
+      else
+        rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), nullptr, d_scal, count, nb, base_offset);
+      if (rc) return rc;
+      if (do_fetch) {
+        rc = fetch_locked(out ? out + b0 * (size_t)(nco * M) : nullptr, is_inf ? is_inf + b0 : nullptr);
+        if (rc) return rc;
+      }
+    }
+    return KZG_GPU_OK;
+  }
+
+  int fetch_locked(uint8_t* out, int* is_inf) {
+    const int nco = last_group == 2 ? 4 : 2;
+    if (last_batch && out)
+      CK(cudaMemcpyAsync(out, out_bytes.p, last_batch * (size_t)(nco * M), cudaMemcpyDeviceToHost, stream));
+    if (last_batch && is_inf)
+      CK(cudaMemcpyAsync(is_inf, out_inf.p, last_batch * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    return KZG_GPU_OK;
+  }
+  int fetch(uint8_t* out, int* is_inf) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    return fetch_locked(out, is_inf);
+  }
+
+  // partial sums for the point-range split (G1 only): XYZZ of the last single MSM
+  int fetch_partial(uint32_t* words, size_t* n_words) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (n_words) *n_words = sizeof(XYZZ<Fp>) / 4;
+    if (!words) return KZG_GPU_OK;
+    if (last_batch != 1 || last_group != 1) return KZG_GPU_ERR_STATE;
+    CK(cudaMemcpyAsync(words, out_xyzz.p, sizeof(XYZZ<Fp>), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    return KZG_GPU_OK;
+  }
+  int sum_partials(const uint32_t* words, uint64_t n, uint8_t* out, int* is_inf) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!words || n == 0 || n > 4096) return KZG_GPU_ERR_ARG;
+    CK(partial.ensure(n * sizeof(XYZZ<Fp>)));
+    CK(out_bytes.ensure(4 * M));
+    CK(out_inf.ensure(sizeof(int)));
+    CK(cudaMemcpyAsync(partial.p, words, n * sizeof(XYZZ<Fp>), cudaMemcpyHostToDevice, stream));
+    sum_points<Fp><<<1, 1, 0, stream>>>(n, partial.as<XYZZ<Fp>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M);
+    LAUNCHED();
+    last_batch = 1;
+    last_group = 1;
+    return fetch_locked(out, is_inf);
+  }
+
+  // ------------------------------------------------------------------ Fr polynomials
+  // coefficients (host bytes) -> poly0 (Montgomery).  Returns with the copy + conversion enqueued.
+  int upload_poly(const uint8_t* coeffs, uint64_t n) {
+    CK(stage.ensure(n * (size_t)SB));
+    CK(poly0.ensure(n * sizeof(Fr)));
+    CK(poly1.ensure(n * sizeof(Fr)));
+    CK(cudaMemcpyAsync(stage.p, coeffs, n * (size_t)SB, cudaMemcpyHostToDevice, stream));
+    unsigned grid = (unsigned)std::min<uint64_t>((n + 127) / 128, 148 * 8);
+    fr_from_bytes<C><<<grid, 128, 0, stream>>>(n, stage.as<uint8_t>(), poly0.as<Fr>());
+    LAUNCHED();
+    return KZG_GPU_OK;
+  }
+  // quotient of poly0 by the k consecutive roots -> qbytes (device, (n-k)*SB bytes)
+  int enqueue_quotient(uint64_t n, int64_t first_root, uint64_t k) {
+    constexpr int QT = 512;
+    poly_quotient_rounds<C, QT><<<1, QT, 0, stream>>>(n, (long long)first_root, k, poly0.as<Fr>(), poly1.as<Fr>());
+    LAUNCHED();
+    const Fr* q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
+    const uint64_t nq = n - k;
+    CK(qbytes.ensure(nq * (size_t)SB));
+    unsigned grid = (unsigned)std::min<uint64_t>((nq + 127) / 128, 148 * 8);
+    fr_to_bytes<C><<<grid, 128, 0, stream>>>(nq, q, qbytes.as<uint8_t>());
+    LAUNCHED();
+    return KZG_GPU_OK;
+  }
+
+  int poly_quotient(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!coeffs || !q_out || n == 0 || k >= n) return KZG_GPU_ERR_ARG;
+    int rc = upload_poly(coeffs, n);
+    if (rc) return rc;
+    rc = enqueue_quotient(n, first_root, k);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(q_out, qbytes.p, (n - k) * (size_t)SB, cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    return KZG_GPU_OK;
+  }
+
+  int poly_eval(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* y_out) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!y_out || k == 0 || (n && !coeffs)) return KZG_GPU_ERR_ARG;
+    if (n == 0) { memset(y_out, 0, k * (size_t)SB); return KZG_GPU_OK; }
+    int rc = upload_poly(coeffs, n);
+    if (rc) return rc;
+    CK(poly1.ensure(k * sizeof(Fr)));
+    CK(qbytes.ensure(k * (size_t)SB));
+    constexpr int ET = 128;
+    unsigned grid = (unsigned)std::min<uint64_t>(k, 148 * 16);
+    poly_eval_range_kernel<C, ET><<<grid, ET, 0, stream>>>(n, (long long)first_root, k, poly0.as<Fr>(), poly1.as<Fr>());
+    LAUNCHED();
+    fr_to_bytes<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(k, poly1.as<Fr>(), qbytes.as<uint8_t>());
+    LAUNCHED();
+    CK(cudaMemcpyAsync(y_out, qbytes.p, k * (size_t)SB, cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    return KZG_GPU_OK;
+  }
+
+  // create_proof: quotient stays on device and feeds the MSM directly
+  int prove(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out, int* is_inf) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (srs_n == 0) return KZG_GPU_ERR_STATE;
+    if ((n && !coeffs) || k == 0) return KZG_GPU_ERR_ARG;
+    if (k >= n) {  // zero quotient -> point at infinity
+      if (out) memset(out, 0, 2 * M);
+      if (is_inf) *is_inf = 1;
+      return KZG_GPU_OK;
+    }
+    if (n - k > srs_n) return KZG_GPU_ERR_ARG;
+    int rc = upload_poly(coeffs, n);
+    if (rc) return rc;
+    rc = enqueue_quotient(n, first_root, k);
+    if (rc) return rc;
+    // same stream: the MSM is ordered after the quotient; qbytes is not touched by the MSM path
+    return msm(1, qbytes.as<uint8_t>(), true, n - k, 1, 0, out, is_inf, true);
+  }
+
+  // ------------------------------------------------------------------ trusted setup
+  int ensure_fixed_base_tables() {
+    if (fb_ready) return KZG_GPU_OK;
+    constexpr int W = fb_windows<C>();
+    CK(fb1.ensure((size_t)W * FB_HALF * sizeof(Affine<Fp>)));
+    CK(fb2.ensure((size_t)W * FB_HALF * sizeof(Affine<Fp2>)));
+    Affine<Fp> gen1;
+    Affine<Fp2> gen2;
+    for (int i = 0; i < Fp::L; i++) {
+      gen1.x.v[i] = C::g1x(i); gen1.y.v[i] = C::g1y(i);
+      gen2.x.a.v[i] = C::g2xa(i); gen2.x.b.v[i] = C::g2xb(i);
+      gen2.y.a.v[i] = C::g2ya(i); gen2.y.b.v[i] = C::g2yb(i);
+    }
+    const unsigned grid = (W * FB_HALF + 63) / 64;
+    fixed_base_table<C, Fp><<<grid, 64, 0, stream>>>(gen1, fb1.as<Affine<Fp>>());
+    LAUNCHED();
+    fixed_base_table<C, Fp2><<<grid, 64, 0, stream>>>(gen2, fb2.as<Affine<Fp2>>());
+    LAUNCHED();
+    CK(cudaStreamSynchronize(stream));
+    fb_ready = true;
+    return KZG_GPU_OK;
+  }
+
+  int setup_powers(const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!s_le || n == 0) return KZG_GPU_ERR_ARG;
+    int rc = ensure_fixed_base_tables();
+    if (rc) return rc;
+    CK(stage.ensure(std::max<size_t>(n * (size_t)(4 * M), 64)));
+    CK(powers.ensure(n * sizeof(Fr)));
+    CK(g1.ensure(n * sizeof(Affine<Fp>)));
+    CK(g2.ensure(n * sizeof(Affine<Fp2>)));
+    CK(scal.ensure(64));
+    CK(cudaMemcpyAsync(scal.p, s_le, SB, cudaMemcpyHostToDevice, stream));
+    const int per_thread = 32;
+    const uint64_t nthreads = (n + per_thread - 1) / per_thread;
+    setup_powers_kernel<C><<<(unsigned)((nthreads + 63) / 64), 64, 0, stream>>>(n, scal.as<uint8_t>(), per_thread, powers.as<uint32_t>());
+    LAUNCHED();
+    const unsigned grid = (unsigned)((n + 127) / 128);
+    fixed_base_mul<C, Fp><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb1.as<Affine<Fp>>(), g1.as<Affine<Fp>>(),
+                                                    g1_out ? stage.as<uint8_t>() : nullptr, M);
+    LAUNCHED();
+    if (g1_out) CK(cudaMemcpyAsync(g1_out, stage.p, n * (size_t)(2 * M), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    fixed_base_mul<C, Fp2><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb2.as<Affine<Fp2>>(), g2.as<Affine<Fp2>>(),
+                                                     g2_out ? stage.as<uint8_t>() : nullptr, M);
+    LAUNCHED();
+    if (g2_out) CK(cudaMemcpyAsync(g2_out, stage.p, n * (size_t)(4 * M), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    srs_n = n;
+    have_g2 = true;
+    return build_table();
+  }
+
+  // ------------------------------------------------------------------ diagnostics
+  int microbench(int kind, double* ops) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!ops || kind < 0 || kind > 3) return KZG_GPU_ERR_ARG;
+    CK(scal.ensure(64));
+    const int blocks = 148 * 8, threads = 256;
+    int iters = kind <= 1 ? 4096 : 256;
+    double per_thread_iter = kind == 0 ? 32.0 : kind == 1 ? 16.0 : 2.0;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+      CK(cudaEventRecord(e0, stream));
+      switch (kind) {
+        case 0: bench_wide_chain<<<blocks, threads, 0, stream>>>(iters, 12345u + rep, scal.as<uint32_t>()); break;
+        case 1: bench_imad32<<<blocks, threads, 0, stream>>>(iters, 12345u + rep, scal.as<uint32_t>()); break;
+        case 2: bench_modmul<Fp><<<blocks, threads, 0, stream>>>(iters, 12345u + rep, scal.as<uint32_t>()); break;
+        default: bench_modmul<Fr><<<blocks, threads, 0, stream>>>(iters, 12345u + rep, scal.as<uint32_t>()); break;
+      }
+      LAUNCHED();
+      CK(cudaEventRecord(e1, stream));
+      CK(cudaEventSynchronize(e1));
+      float ms = 0;
+      CK(cudaEventElapsedTime(&ms, e0, e1));
+      if (rep > 0) best = std::min(best, ms);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ops = (double)blocks * threads * iters * per_thread_iter / (best * 1e-3);
+    return KZG_GPU_OK;
+  }
+
+  int selftest(int* failures) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!failures) return KZG_GPU_ERR_ARG;
+    CK(out_inf.ensure(sizeof(int)));
+    CK(cudaMemsetAsync(out_inf.p, 0, sizeof(int), stream));
+    selftest_kernel<C><<<4, 32, 0, stream>>>(20261104u, out_inf.as<int>());
+    LAUNCHED();
+    CK(cudaMemcpyAsync(failures, out_inf.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    return KZG_GPU_OK;
+  }
+};
+
+
+// factories, one per translation unit
+kzg_gpu_ctx* kzg_gpu_make_ctx_bn158(int device, int* rc);
+kzg_gpu_ctx* kzg_gpu_make_ctx_bn254(int device, int* rc);
+kzg_gpu_ctx* kzg_gpu_make_ctx_bls12381(int device, int* rc);
+
+#define KZG_GPU_DEFINE_FACTORY(fn, CURVE)                         \
+  kzg_gpu_ctx* fn(int device, int* rc) {                          \
+    auto* p = new (std::nothrow) Ctx<kzgb200::CURVE>();           \
+    if (!p) { *rc = KZG_GPU_ERR_MEMORY; return nullptr; }         \
+    p->device = device;                                           \
+    *rc = p->init();                                              \
+    if (*rc) { delete p; return nullptr; }                        \
+    return p;                                                     \
+  }

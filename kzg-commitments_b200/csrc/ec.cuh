@@ -35,7 +35,7 @@ struct XYZZ {
   }
 
   // 2 * (affine p) -> XYZZ   (mdbl-2008-s-1)
-  KZG_HD static XYZZ dbl_affine(const F& x, const F& y) {
+  KZG_HDN static XYZZ dbl_affine(const F& x, const F& y) {
     F U = F::dbl(y);
     F V = F::sqr(U);
     F W = F::mul(U, V);
@@ -51,7 +51,7 @@ struct XYZZ {
   }
 
   // this = 2 * this   (dbl-2008-s-1, a = 0)
-  KZG_HD void dbl() {
+  KZG_HDN void dbl() {
     if (is_inf()) return;
     F U = F::dbl(Y);
     F V = F::sqr(U);
@@ -68,7 +68,7 @@ struct XYZZ {
   }
 
   // this += (x, y) with y already carrying the digit's sign   (madd-2008-s)
-  KZG_HD void madd(const F& x, const F& y) {
+  KZG_HDN void madd(const F& x, const F& y) {
     if (x.is_zero() && y.is_zero()) return;  // affine infinity
     if (is_inf()) {
       X = x; Y = y; ZZ = F::one(); ZZZ = F::one();
@@ -96,7 +96,7 @@ struct XYZZ {
   KZG_HD void madd(const Affine<F>& p, bool negate) { madd(p.x, negate ? F::neg(p.y) : p.y); }
 
   // this += o   (add-2008-s)
-  KZG_HD void add(const XYZZ& o) {
+  KZG_HDN void add(const XYZZ& o) {
     if (o.is_inf()) return;
     if (is_inf()) { *this = o; return; }
     F U1 = F::mul(X, o.ZZ);
@@ -124,7 +124,7 @@ struct XYZZ {
   KZG_HD void negate() { Y = F::neg(Y); }
 
   // x = X/ZZ, y = Y/ZZZ with one field inversion (replaces ECP_affine, ecp.cpp:329-348)
-  KZG_HD Affine<F> to_affine() const {
+  KZG_HDN Affine<F> to_affine() const {
     if (is_inf()) return Affine<F>::inf();
     F i3 = F::inv(ZZZ);               // 1/Z^3
     F i1 = F::mul(ZZ, i3);            // 1/Z
@@ -135,7 +135,7 @@ struct XYZZ {
 
 // k * P by double-and-add over the bits of a little-endian word array (setup / fix-ups / tests)
 template <class F>
-KZG_HD XYZZ<F> scalar_mul_bits(const Affine<F>& p, const uint32_t* k, int nbits) {
+KZG_HDN XYZZ<F> scalar_mul_bits(const Affine<F>& p, const uint32_t* k, int nbits) {
   XYZZ<F> acc = XYZZ<F>::inf();
   for (int i = nbits - 1; i >= 0; i--) {
     acc.dbl();

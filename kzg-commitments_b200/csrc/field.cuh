@@ -134,7 +134,7 @@ struct Field {
 
   // a^(p-2) by square-and-multiply over the constant exponent (replaces FP_inv, fp.cpp:817-840).
   // inv(0) = 0.
-  KZG_HD static Field inv(const Field& a) {
+  KZG_HDN static Field inv(const Field& a) {
     Field r = one();
     for (int i = P::BITS - 1; i >= 0; i--) {
       r = sqr(r);

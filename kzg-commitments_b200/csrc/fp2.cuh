@@ -35,7 +35,7 @@ struct Field2 {
     Base t1 = Base::mul(x.a, x.b);
     return Field2{t0, Base::dbl(t1)};
   }
-  KZG_HD static Field2 inv(const Field2& x) {
+  KZG_HDN static Field2 inv(const Field2& x) {
     Base n = Base::inv(Base::add(Base::sqr(x.a), Base::sqr(x.b)));
     return Field2{Base::mul(x.a, n), Base::neg(Base::mul(x.b, n))};
   }

@@ -249,7 +249,7 @@ msm_reduce_groups(int cpg, const XYZZ<F>* __restrict__ chunk_out, XYZZ<F>* __res
 
 // big-endian canonical bytes of a field element (MODBYTES each), as FP_toBytes / BIG_toBytes write them
 template <class P>
-KZG_HD void fe_to_be_bytes(const Field<P>& mont, uint8_t* out, int modbytes) {
+KZG_HDN void fe_to_be_bytes(const Field<P>& mont, uint8_t* out, int modbytes) {
   Field<P> c = Field<P>::from_mont(mont);
   for (int j = 0; j < modbytes; j++) {
     int bytepos = modbytes - 1 - j;  // little-endian byte index
@@ -257,7 +257,7 @@ KZG_HD void fe_to_be_bytes(const Field<P>& mont, uint8_t* out, int modbytes) {
   }
 }
 template <class P>
-KZG_HD Field<P> fe_from_be_bytes(const uint8_t* in, int modbytes) {
+KZG_HDN Field<P> fe_from_be_bytes(const uint8_t* in, int modbytes) {
   Field<P> c = Field<P>::zero();
   for (int j = 0; j < modbytes; j++) {
     int bytepos = modbytes - 1 - j;
@@ -297,7 +297,7 @@ template <class P> struct CoordCount<Field2<P>> { static constexpr int value = 4
 
 // ---------------------------------------------------------------- 6. finish
 // One thread per MSM of the batch: Horner over its window groups, optional extra terms, affine, bytes.
-// out_xyzz (optional) receives the projective result instead (used by the multi-GPU partial sums).
+// out_xyzz (optional) also receives the projective result (used by the multi-GPU partial sums).
 template <class F>
 __global__ void msm_finish(uint64_t batch, int groups_per_msm, int c, const XYZZ<F>* __restrict__ group_out,
                            uint8_t* __restrict__ out_bytes, int* __restrict__ is_inf, int modbytes,
@@ -309,7 +309,7 @@ __global__ void msm_finish(uint64_t batch, int groups_per_msm, int c, const XYZZ
     for (int k = 0; k < c; k++) acc.dbl();
     acc.add(group_out[m * groups_per_msm + g]);
   }
-  if (out_xyzz) { out_xyzz[m] = acc; return; }
+  if (out_xyzz) out_xyzz[m] = acc;
   const Affine<F> a = acc.to_affine();
   const int nbytes = CoordCount<F>::value * modbytes;
   if (acc.is_inf()) {
@@ -318,6 +318,23 @@ __global__ void msm_finish(uint64_t batch, int groups_per_msm, int c, const XYZZ
   } else {
     affine_to_bytes(a, out_bytes + m * nbytes, modbytes);
     is_inf[m] = 0;
+  }
+}
+
+// out = sum of n projective points (the fold of the per-GPU partial sums of a point-range split)
+template <class F>
+__global__ void sum_points(uint64_t n, const XYZZ<F>* __restrict__ pts, uint8_t* __restrict__ out_bytes,
+                           int* __restrict__ is_inf, int modbytes) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  XYZZ<F> acc = XYZZ<F>::inf();
+  for (uint64_t i = 0; i < n; i++) acc.add(pts[i]);
+  const int nbytes = CoordCount<F>::value * modbytes;
+  if (acc.is_inf()) {
+    for (int j = 0; j < nbytes; j++) out_bytes[j] = 0;
+    is_inf[0] = 1;
+  } else {
+    affine_to_bytes(acc.to_affine(), out_bytes, modbytes);
+    is_inf[0] = 0;
   }
 }
 

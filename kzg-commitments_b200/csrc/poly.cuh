@@ -36,7 +36,7 @@ KZG_D void fr_store(uint8_t* dst, uint64_t idx, const Field<typename C::FrP>& m)
 
 // (first_root + j) mod r in Montgomery form; first_root may be negative
 template <class C>
-KZG_D Field<typename C::FrP> fr_from_i64(long long x) {
+__device__ __noinline__ Field<typename C::FrP> fr_from_i64(long long x) {
   using Fr = Field<typename C::FrP>;
   Fr k = Fr::zero();
   unsigned long long mag = x < 0 ? (unsigned long long)(-(x + 1)) + 1ull : (unsigned long long)x;
@@ -47,7 +47,7 @@ KZG_D Field<typename C::FrP> fr_from_i64(long long x) {
 }
 
 template <class Fr>
-KZG_D Fr fr_pow_u32(Fr base, uint32_t e) {
+__device__ __noinline__ Fr fr_pow_u32(Fr base, uint32_t e) {
   Fr r = Fr::one();
   while (e) {
     if (e & 1) r = Fr::mul(r, base);

@@ -15,9 +15,14 @@
 #if defined(__CUDACC__)
 #define KZG_HD __host__ __device__ __forceinline__
 #define KZG_D __device__ __forceinline__
+// group-law level routines are real calls: forcing ~10-40 inlined Montgomery products into every
+// call site makes NVVM's compile time explode and buys nothing (a call costs a few cycles per ~4000
+// instructions of work).  The hot accumulate loop opts back in explicitly where it matters.
+#define KZG_HDN __host__ __device__ __noinline__
 #else
 #define KZG_HD inline
 #define KZG_D inline
+#define KZG_HDN __attribute__((noinline))
 #endif
 
 namespace kzgb200 {

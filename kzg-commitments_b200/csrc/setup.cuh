@@ -16,12 +16,12 @@ constexpr int FB_C = 8;                       // fixed-base window bits
 constexpr int FB_HALF = 1 << (FB_C - 1);      // 128 table entries per window
 
 template <class C>
-constexpr int fb_windows() { return (C::SCALAR_BITS + 1 + FB_C - 1) / FB_C; }
+KZG_HD constexpr int fb_windows() { return (C::SCALAR_BITS + 1 + FB_C - 1) / FB_C; }
 
 // powers[i] = s^i (canonical little-endian words, NOT Montgomery), i < n.
 // Thread t produces indices [t*S, (t+1)*S): s^(t*S) by square-and-multiply, then S-1 products.
 template <class C>
-__global__ void setup_powers(uint64_t n, const uint8_t* __restrict__ s_bytes, int per_thread,
+__global__ void setup_powers_kernel(uint64_t n, const uint8_t* __restrict__ s_bytes, int per_thread,
                              uint32_t* __restrict__ powers /* n * FrP::L words */) {
   using Fr = Field<typename C::FrP>;
   const uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
