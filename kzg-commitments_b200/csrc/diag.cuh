@@ -10,7 +10,7 @@ namespace kzgb200 {
 #if defined(__CUDACC__)
 // kind 0: rows of 8 lo/hi multiply-add pairs with one carry chain per row (what mul() issues);
 // 4 independent rows per thread.  products = threads * iters * 32.
-__global__ void __launch_bounds__(256) bench_wide_chain(int iters, uint32_t seed, uint32_t* sink) {
+static __global__ void __launch_bounds__(256) bench_wide_chain(int iters, uint32_t seed, uint32_t* sink) {
   uint32_t acc[4][16];
   uint32_t a[8];
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256) bench_wide_chain(int iters, uint32_t seed
 }
 
 // kind 1: independent 32-bit IMAD (mad.lo.u32), 16 accumulators per thread. ops = threads*iters*16
-__global__ void __launch_bounds__(256) bench_imad32(int iters, uint32_t seed, uint32_t* sink) {
+static __global__ void __launch_bounds__(256) bench_imad32(int iters, uint32_t seed, uint32_t* sink) {
   uint32_t acc[16];
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
 #pragma unroll

@@ -1,0 +1,282 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (include/kzg_gpu.h) via the Python mirror
+of kzg.h, against (a) the golden vectors produced by the UNMODIFIED reference (tests/golden, bit-exact on
+commit.serialize(), proof.serialize(), polyeval_G2, quotient and evaluation bytes), (b) the CPU oracle on
+seeded inputs, (c) size-independent properties at full size, and (d) the reference's own verify_proof
+(oracle/_ref/kzgref-<curve>, prebuilt) accepting GPU proofs and refuting tampered data.
+Everything here is exact integer arithmetic: the bar is byte equality."""
+import os
+import random
+import subprocess
+import sys
+import tempfile
+
+import pytest
+
+from oracle.kzg_oracle import get_curve
+from tests.golden_util import CURVE_NAMES, ROOT, load
+
+sys.path.insert(0, os.path.join(ROOT, "kzg-commitments_b200"))
+import kzg_b200  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctxs():
+    made = {}
+
+    def get(cname):
+        if cname not in made:
+            made[cname] = kzg_b200.Context(cname, 0)
+        return made[cname]
+
+    yield get
+    for c in made.values():
+        c.close()
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_device_selftest(ctxs, cname):
+    assert ctxs(cname).selftest() == 0
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+@pytest.mark.parametrize("precompute", [0, 1])
+def test_golden_vectors_bit_exact(ctxs, cname, precompute):
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    kat, srs = load(cname)
+    ctx.set_option("precompute", precompute)
+    ctx.set_option("window_bits", 5 if precompute else 0)
+    ts = kzg_b200.TrustedSetup.from_file_bytes(cname, srs, ctx=ctx)
+    assert ts.export_setup() == srs
+    for case in kat["cases"]:
+        P = kzg_b200.Poly(ctx, bytes.fromhex(case["coeffs"]))
+        assert P.serialize().hex() == case["polyser"], case["name"]
+        assert kzg_b200.Poly.deserialize((ctx.SB, ctx.r), P.serialize()).coeffs == P.coeffs
+        commit = ts.create_commit(P)
+        assert commit.serialize().hex() == case["commit"], case["name"]
+        assert ts.verify_commit(kzg_b200.Commit.deserialize(commit.serialize()), P)
+        if len(P):
+            xy, inf = ctx.msm_g2(P.raw, len(P))
+            assert (b"\x04" + xy).hex() == case["g2msm"][8:], case["name"]
+        for op in case["openings"]:
+            off, k = op["off"], op["k"]
+            proof = ts.create_proof(P, off, k)
+            assert proof.serialize().hex() == op["proof"], (case["name"], off, k)
+            if len(P):
+                assert ts.evaluate(P, off, k).hex() == op["ys"], (case["name"], off, k)
+            if k < len(P):
+                assert ctx.poly_quotient(P.raw, off, k).hex() == op["quotient"], (case["name"], off, k)
+            # the verifier-side MSMs on the reference's own Z and I
+            Z = kzg_b200.Poly(ctx, bytes.fromhex(op["vanishing"]))
+            I = kzg_b200.Poly(ctx, bytes.fromhex(op["interp"]))
+            (zxy, zinf), (ixy, iinf) = ts.verify_proof_msms(Z, I)
+            g1, g2 = C.srs_from_file_bytes(srs)
+            assert zxy == C.g2_to_octet(C.msm(Z.coeffs, g2, g2=True))[1:]
+            assert ixy == C.g1_to_octet(C.msm(I.coeffs, g1))[1:]
+    ctx.set_option("precompute", 0)
+    ctx.set_option("window_bits", 0)
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_setup_powers_matches_oracle(ctxs, cname):
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    s = random.Random(5).randrange(C.r)
+    ts = kzg_b200.TrustedSetup.generate(cname, 9, s, ctx=ctx)
+    g1, g2 = C.setup(s, 9)
+    assert ts.export_setup() == C.srs_to_file_bytes(g1, g2)
+    with pytest.raises(ValueError):
+        kzg_b200.TrustedSetup.generate(cname, 1, s, ctx=ctx)
+
+
+def _reference_verify(cname, srs_bytes, commit, proof, off, ys):
+    binary = os.path.join(ROOT, "oracle", "_ref", f"kzgref-{cname}")
+    if not os.path.exists(binary):
+        pytest.skip("oracle/_ref not built")
+    with tempfile.TemporaryDirectory() as td:
+        paths = {}
+        for name, data in (("srs", srs_bytes), ("cm", commit), ("pf", proof), ("ys", ys)):
+            paths[name] = os.path.join(td, name)
+            open(paths[name], "wb").write(data)
+        out = subprocess.run([binary, "verify", paths["srs"], paths["cm"], paths["pf"], str(off), paths["ys"]],
+                             check=True, capture_output=True, text=True).stdout
+        return int(out.strip())
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_reference_verify_accepts_gpu_proofs(ctxs, cname):
+    """GPU-generated SRS, commit, proof and opened values go through the reference's verify_proof."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(17 + C.id)
+    ts = kzg_b200.TrustedSetup.generate(cname, 300, rng.randrange(C.r), ctx=ctx)
+    srs_bytes = ts.export_setup()
+    P = kzg_b200.Poly(ctx, [rng.randrange(C.r) for _ in range(257)])
+    commit = ts.create_commit(P)
+    for off, k in ((0, 1), (5, 1), (3, 8), (100, 57)):
+        proof = ts.create_proof(P, off, k)
+        ys = ts.evaluate(P, off, k)
+        assert ys == C.scalars_to_bytes(C.poly_eval_range(P.coeffs, off, k))
+        assert _reference_verify(cname, srs_bytes, commit.serialize(), proof.serialize(), off, ys) == 1
+        bad = bytearray(ys)
+        bad[0] ^= 1
+        assert _reference_verify(cname, srs_bytes, commit.serialize(), proof.serialize(), off, bytes(bad)) == 0
+        assert _reference_verify(cname, srs_bytes, commit.serialize(), proof.serialize(), off + 1, ys) == 0
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_msm_degree_4096_vs_oracle_and_options(ctxs, cname):
+    """BASELINE configs 1/2: a degree-4096 commitment.  Oracle check through the known secret:
+    sum c_i [s^i]G = [P(s)]G, one oracle scalar multiplication (size-independent)."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(4096 + C.id)
+    s = rng.randrange(C.r)
+    n = 4200
+    ts = kzg_b200.TrustedSetup.generate(cname, n, s, ctx=ctx)
+    coeffs = [rng.randrange(C.r) for _ in range(4097)]
+    P = kzg_b200.Poly(ctx, coeffs)
+    want = C.serialize_g1(C.mul(C.poly_eval(coeffs, s), C.g1))
+    assert ts.create_commit(P).serialize() == want
+    # every window size / task split / table mode gives the same bytes
+    for wb, pre, chunk in ((8, 0, 7), (11, 0, 64), (13, 1, 16), (10, 1, 1000)):
+        ctx.set_option("window_bits", wb)
+        ctx.set_option("precompute", pre)
+        ctx.set_option("task_chunk", chunk)
+        ctx.srs_load(ts.g1_bytes, ts.g2_bytes)
+        assert ts.create_commit(P).serialize() == want, (wb, pre, chunk)
+    ctx.set_option("window_bits", 0)
+    ctx.set_option("precompute", 0)
+    ctx.set_option("task_chunk", 0)
+    ctx.srs_load(ts.g1_bytes, ts.g2_bytes)
+    # single-point proof: q(s) = (P(s) - P(a)) / (s - a)
+    a = 7
+    qs = (C.poly_eval(coeffs, s) - C.poly_eval(coeffs, a)) * pow(s - a, -1, C.r) % C.r
+    assert ts.create_proof(P, a, 1).serialize() == C.serialize_g1(C.mul(qs, C.g1))
+    # multi-point proof (k = 64) through the vanishing polynomial
+    k, off = 64, 11
+    zs = 1
+    for j in range(k):
+        zs = zs * (s - off - j) % C.r
+    q, I, _ = C.poly_quotient(coeffs, off, k)
+    assert ts.create_proof(P, off, k).serialize() == C.serialize_g1(C.mul(C.poly_eval(q, s), C.g1))
+    assert ctx.poly_quotient(P.raw, off, k) == C.scalars_to_bytes(q)
+    # G2 MSM over 4097 terms (verify_proof's polyeval_G2 at k = 4096)
+    xy, inf = ctx.msm_g2(P.raw, len(P))
+    assert xy == C.g2_to_octet(C.mul(C.poly_eval(coeffs, s), C.g2, g2=True))[1:]
+    # error behaviour of create_commit / create_proof (src/trusted_setup.cpp:138-139, 215-216)
+    with pytest.raises(ValueError):
+        ts.create_commit([1] * n)
+    with pytest.raises(ValueError):
+        ts.create_proof(P, 0, 0)
+    assert ts.create_proof(P, 0, 4097).is_inf and ts.create_proof(P, 0, 5000).is_inf
+
+
+def test_edge_scalars_and_structured_inputs(ctxs):
+    cname = "bls12381"
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(3)
+    s = rng.randrange(C.r)
+    n = 600
+    ts = kzg_b200.TrustedSetup.generate(cname, n + 1, s, ctx=ctx)
+    cases = {
+        "zeros": [0] * n,
+        "ones": [1] * n,
+        "rm1": [C.r - 1] * n,
+        "single": [0] * (n - 1) + [rng.randrange(1, C.r)],
+        "half_zero": [rng.randrange(C.r) if i % 2 else 0 for i in range(n)],
+        "small": [rng.randrange(256) for _ in range(n)],
+        "pow2": [1 << (i % 255) for i in range(n)],
+    }
+    for name, sc in cases.items():
+        raw = C.scalars_to_bytes(sc)
+        xy, inf = ctx.msm_g1(raw, n)
+        want = C.mul(C.poly_eval(sc, s), C.g1) if any(sc) else None
+        assert xy == C.g1_to_octet(want)[1:], name
+        assert inf == (want is None), name
+    # non-canonical scalars (>= r) are reduced like PAIR_G1mul's BIG_mod
+    sc = [(1 << 256) - 1 - i for i in range(40)]
+    raw = b"".join(v.to_bytes(32, "little") for v in sc)
+    xy, _ = ctx.msm_g1(raw, 40)
+    assert xy == C.g1_to_octet(C.mul(C.poly_eval([v % C.r for v in sc], s), C.g1))[1:]
+    # a degenerate SRS (secret 1: every base is the generator) drives the doubling / cancellation branches
+    ts1 = kzg_b200.TrustedSetup.generate(cname, 64, 1, ctx=ctx)
+    sc = [5] * 20 + [C.r - 5] * 20 + [3] * 10
+    xy, inf = ctx.msm_g1(C.scalars_to_bytes(sc), len(sc))
+    assert xy == C.g1_to_octet(C.mul(30, C.g1))[1:]
+    xy, inf = ctx.msm_g1(C.scalars_to_bytes([9] * 8 + [C.r - 9] * 8), 16)
+    assert inf and xy == bytes(96)
+    # base_offset, empty input
+    ts = kzg_b200.TrustedSetup.generate(cname, 50, s, ctx=ctx)
+    sc = [rng.randrange(C.r) for _ in range(10)]
+    xy, _ = ctx.msm_g1(C.scalars_to_bytes(sc), 10, base_offset=7)
+    assert xy == C.g1_to_octet(C.mul(C.poly_eval(sc, s) * pow(s, 7, C.r), C.g1))[1:]
+    xy, inf = ctx.msm_g1(b"", 0)
+    assert inf and xy == bytes(96)
+    with pytest.raises(RuntimeError):
+        ctx.msm_g1(C.scalars_to_bytes(sc), 10, base_offset=45)
+
+
+def test_batch_and_point_range_split(ctxs):
+    """BASELINE config 3 (batched blob commitments) and config 4 (point-range split + partial-sum fold)."""
+    cname = "bls12381"
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(8)
+    s = rng.randrange(C.r)
+    n, batch = 1024, 6
+    ts = kzg_b200.TrustedSetup.generate(cname, n, s, ctx=ctx)
+    blobs = [[rng.randrange(C.r) for _ in range(n)] for _ in range(batch)]
+    blobs[2] = [0] * n
+    raw = b"".join(C.scalars_to_bytes(b) for b in blobs)
+    out, infs = ctx.msm_g1_batch(raw, n, batch)
+    for b in range(batch):
+        want = C.mul(C.poly_eval(blobs[b], s), C.g1) if any(blobs[b]) else None
+        assert out[b * 96:(b + 1) * 96] == C.g1_to_octet(want)[1:], b
+        assert infs[b] == (want is None)
+    # split one MSM by point range into 4 shards, fold the projective partial sums
+    full, _ = ctx.msm_g1(C.scalars_to_bytes(blobs[0]), n)
+    partials = []
+    for g in range(4):
+        lo, hi = g * n // 4, (g + 1) * n // 4
+        ctx.msm_g1(C.scalars_to_bytes(blobs[0][lo:hi]), hi - lo, base_offset=lo)
+        partials.append(ctx.msm_fetch_partial())
+    xy, inf = ctx.g1_sum_partials(partials)
+    assert xy == full and not inf
+
+
+def test_msm_2_16_linearity_and_oracle(ctxs):
+    """Config 4 at 2^16: [P(s)]G check plus linearity MSM(a) + MSM(b) = MSM(a+b) at full size."""
+    cname = "bls12381"
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(16)
+    s = rng.randrange(C.r)
+    n = 1 << 16
+    ctx.setup_powers(s, n, want_bytes=False)
+    a = [rng.randrange(C.r) for _ in range(n)]
+    b = [rng.randrange(C.r) for _ in range(n)]
+    ab = [(x + y) % C.r for x, y in zip(a, b)]
+
+    def ps(v):
+        acc, si = 0, 1
+        for c in v:
+            acc = (acc + c * si) % C.r
+            si = si * s % C.r
+        return acc
+
+    xa, _ = ctx.msm_g1(C.scalars_to_bytes(a), n)
+    assert xa == C.g1_to_octet(C.mul(ps(a), C.g1))[1:]
+    xab, _ = ctx.msm_g1(C.scalars_to_bytes(ab), n)
+    xb, _ = ctx.msm_g1(C.scalars_to_bytes(b), n)
+    A = (int.from_bytes(xa[:48], "big"), int.from_bytes(xa[48:], "big"))
+    B = (int.from_bytes(xb[:48], "big"), int.from_bytes(xb[48:], "big"))
+    assert xab == C.g1_to_octet(C.add(A, B))[1:]
+    ctx.set_option("precompute", 1)
+    ctx.setup_powers(s, n, want_bytes=False)
+    xa2, _ = ctx.msm_g1(C.scalars_to_bytes(a), n)
+    ctx.set_option("precompute", 0)
+    assert xa2 == xa
