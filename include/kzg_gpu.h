@@ -63,7 +63,8 @@ int kzg_gpu_ctx_create(kzg_gpu_ctx** out, int curve, int device);
 void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
 
 /* Tunables (mostly for bench/tests): "window_bits" (0 = auto), "precompute" (0/1: build the
- * per-SRS window table at srs_load), "task_chunk", "reduce_chunk".  Takes effect at the next srs_load / MSM. */
+ * per-SRS window table at srs_load), "task_chunk", "reduce_chunk", "setup_g2" (0: setup_powers with a NULL
+ * g2_out generates a G1-only SRS).  Takes effect at the next srs_load / setup_powers / MSM. */
 int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value);
 
 /* Make an SRS resident.  g1: n * 2M bytes.  g2: n * 4M bytes or NULL (G1-only use). */

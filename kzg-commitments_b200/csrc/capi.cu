@@ -63,6 +63,7 @@ int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value) {
   std::string n(name);
   if (n == "window_bits") { if (value != 0 && (value < 2 || value > 22)) return KZG_GPU_ERR_ARG; ctx->opt_window_bits = (int)value; }
   else if (n == "precompute") ctx->opt_precompute = value ? 1 : 0;
+  else if (n == "setup_g2") ctx->opt_setup_g2 = value ? 1 : 0;
   else if (n == "task_chunk") { if (value < 0 || value > (1 << 20)) return KZG_GPU_ERR_ARG; ctx->opt_task_chunk = (int)value; }
   else if (n == "reduce_chunk") { if (value < 0 || (value & (value - 1))) return KZG_GPU_ERR_ARG; ctx->opt_reduce_chunk = (int)value; }
   else return KZG_GPU_ERR_ARG;

@@ -63,7 +63,7 @@ struct kzg_gpu_ctx {
   uint64_t launches = 0;
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
-  int opt_window_bits = 0, opt_precompute = 0, opt_task_chunk = 0, opt_reduce_chunk = 0;
+  int opt_window_bits = 0, opt_precompute = 0, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1;
 
   virtual ~kzg_gpu_ctx() {}
   virtual int srs_load(uint64_t n, const uint8_t* g1, const uint8_t* g2) = 0;
@@ -470,7 +470,6 @@ struct Ctx final : kzg_gpu_ctx {
     CK(stage.ensure(std::max<size_t>(n * (size_t)(4 * M), 64)));
     CK(powers.ensure(n * sizeof(Fr)));
     CK(g1.ensure(n * sizeof(Affine<Fp>)));
-    CK(g2.ensure(n * sizeof(Affine<Fp2>)));
     CK(scal.ensure(64));
     CK(cudaMemcpyAsync(scal.p, s_le, SB, cudaMemcpyHostToDevice, stream));
     const int per_thread = 32;
@@ -483,13 +482,17 @@ struct Ctx final : kzg_gpu_ctx {
     LAUNCHED();
     if (g1_out) CK(cudaMemcpyAsync(g1_out, stage.p, n * (size_t)(2 * M), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
-    fixed_base_mul<C, Fp2><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb2.as<Affine<Fp2>>(), g2.as<Affine<Fp2>>(),
-                                                     g2_out ? stage.as<uint8_t>() : nullptr, M);
-    LAUNCHED();
-    if (g2_out) CK(cudaMemcpyAsync(g2_out, stage.p, n * (size_t)(4 * M), cudaMemcpyDeviceToHost, stream));
-    CK(cudaStreamSynchronize(stream));
+    const bool want_g2 = g2_out || opt_setup_g2;  // "setup_g2" = 0: G1-only SRS (large synthetic MSM benches)
+    if (want_g2) {
+      CK(g2.ensure(n * sizeof(Affine<Fp2>)));
+      fixed_base_mul<C, Fp2><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb2.as<Affine<Fp2>>(), g2.as<Affine<Fp2>>(),
+                                                       g2_out ? stage.as<uint8_t>() : nullptr, M);
+      LAUNCHED();
+      if (g2_out) CK(cudaMemcpyAsync(g2_out, stage.p, n * (size_t)(4 * M), cudaMemcpyDeviceToHost, stream));
+      CK(cudaStreamSynchronize(stream));
+    }
     srs_n = n;
-    have_g2 = true;
+    have_g2 = want_g2;
     return build_table();
   }
 
