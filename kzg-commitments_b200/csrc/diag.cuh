@@ -68,8 +68,8 @@ __global__ void __launch_bounds__(256) bench_modmul(int iters, uint32_t seed, ui
   x.v[0] ^= (seed * (tid + 1)) & 0xffff;
   z.v[0] ^= (seed * (tid + 7)) & 0xffff;
   for (int it = 0; it < iters; it++) {
-    x = F::mul(x, y);
-    z = F::mul(z, y);
+    x = F::mul_inline(x, y);
+    z = F::mul_inline(z, y);
   }
   uint32_t o = 0;
 #pragma unroll

@@ -92,7 +92,14 @@ struct Field {
   KZG_HD static Field neg(const Field& a) { return sub(zero(), a); }
 
   // ---- Montgomery product a*b/R mod p, inputs and output canonical.
-  KZG_HD static Field mul(const Field& a, const Field& b) {
+  // mul() is ONE out-of-line routine per field (operands by value: ptxas passes the 2*L words in
+  // registers, no stack traffic).  Inlining the ~2L^2 multiply-adds at every call site made the
+  // group-law code tens of KiB per routine and the bucket-accumulation kernel instruction-fetch
+  // bound (ncu: stall_no_instruction 4.3 of 9.4 cycles per issue, profiles/r1_accumulate_v1.md);
+  // with the call the hot loop fits the instruction cache.  mul_inline() is the same body for
+  // call sites that want it fused (the modmul microbenchmark).
+  KZG_HDN static Field mul(Field a, Field b) { return mul_inline(a, b); }
+  KZG_HD static Field mul_inline(const Field& a, const Field& b) {
     static_assert(L % 2 == 0, "even limb count required");
     uint32_t ev[L], od[L];
     // row 0: ev = a_even * b0 (pairs j,j+1 for even j) ; od = a_odd * b0 (value at limb offset 1)

@@ -47,7 +47,7 @@ def test_golden_vectors_bit_exact(ctxs, cname, precompute):
     ctx = ctxs(cname)
     kat, srs = load(cname)
     ctx.set_option("precompute", precompute)
-    ctx.set_option("window_bits", 5 if precompute else 0)
+    ctx.set_option("window_bits", 7 if precompute else 0)
     ts = kzg_b200.TrustedSetup.from_file_bytes(cname, srs, ctx=ctx)
     assert ts.export_setup() == srs
     for case in kat["cases"]:
