@@ -62,8 +62,9 @@ int kzg_gpu_scalar_bytes(int curve);
 int kzg_gpu_ctx_create(kzg_gpu_ctx** out, int curve, int device);
 void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
 
-/* Tunables (mostly for bench/tests): "window_bits" (0 = auto), "precompute" (0/1: build the
- * per-SRS window table at srs_load), "task_chunk", "reduce_chunk", "setup_g2" (0: setup_powers with a NULL
+/* Tunables (mostly for bench/tests): "window_bits" (0 = auto), "precompute" (0: none, 1: build the per-SRS
+ * G1 window table T[w][i] = 2^(c*w) G_i at srs_load / setup_powers, 2: also for G2), "profile" (record
+ * per-phase CUDA events, see kzg_gpu_phase_times), "task_chunk", "reduce_chunk", "setup_g2" (0: setup_powers with a NULL
  * g2_out generates a G1-only SRS).  Takes effect at the next srs_load / setup_powers / MSM. */
 int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value);
 
@@ -111,6 +112,10 @@ int kzg_gpu_prove(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t f
 void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 uint64_t kzg_gpu_launch_count(const kzg_gpu_ctx* ctx);
+
+/* With the "profile" option set: CUDA-event durations (ms) of the most recent MSM pass, ms[0..3] =
+ * digits+sort+tasks, bucket accumulation, bucket reduction, finish (affine + bytes).  n >= 4. */
+int kzg_gpu_phase_times(kzg_gpu_ctx* ctx, float* ms, int n);
 
 /* Integer-pipe microbenchmarks used for the roofline denominator:
  * kind 0: independent mad.lo.cc/madc.hi.cc chains (-> IMAD.WIDE.U32.X), returns 32x32 products/s

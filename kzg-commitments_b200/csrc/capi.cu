@@ -62,7 +62,8 @@ int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value) {
   if (!ctx || !name) return KZG_GPU_ERR_ARG;
   std::string n(name);
   if (n == "window_bits") { if (value != 0 && (value < 2 || value > 22)) return KZG_GPU_ERR_ARG; ctx->opt_window_bits = (int)value; }
-  else if (n == "precompute") ctx->opt_precompute = value ? 1 : 0;
+  else if (n == "precompute") { if (value < 0 || value > 2) return KZG_GPU_ERR_ARG; ctx->opt_precompute = (int)value; }
+  else if (n == "profile") ctx->opt_profile = value ? 1 : 0;
   else if (n == "setup_g2") ctx->opt_setup_g2 = value ? 1 : 0;
   else if (n == "task_chunk") { if (value < 0 || value > (1 << 20)) return KZG_GPU_ERR_ARG; ctx->opt_task_chunk = (int)value; }
   else if (n == "reduce_chunk") { if (value < 0 || (value & (value - 1))) return KZG_GPU_ERR_ARG; ctx->opt_reduce_chunk = (int)value; }
@@ -110,6 +111,7 @@ int kzg_gpu_prove(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t f
 void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 uint64_t kzg_gpu_launch_count(const kzg_gpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
 int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops) { return ctx ? ctx->microbench(kind, ops) : KZG_GPU_ERR_ARG; }
+int kzg_gpu_phase_times(kzg_gpu_ctx* ctx, float* ms, int n) { return ctx ? ctx->phase_times(ms, n) : KZG_GPU_ERR_ARG; }
 int kzg_gpu_selftest(kzg_gpu_ctx* ctx, int* failures) { return ctx ? ctx->selftest(failures) : KZG_GPU_ERR_ARG; }
 
 }  // extern "C"

@@ -63,7 +63,9 @@ struct kzg_gpu_ctx {
   uint64_t launches = 0;
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
-  int opt_window_bits = 0, opt_precompute = 0, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1;
+  int opt_window_bits = 0, opt_precompute = 1, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
+      opt_profile = 0;
+  cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
   virtual int srs_load(uint64_t n, const uint8_t* g1, const uint8_t* g2) = 0;
@@ -78,6 +80,7 @@ struct kzg_gpu_ctx {
   virtual int prove(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out, int* is_inf) = 0;
   virtual int microbench(int kind, double* ops) = 0;
   virtual int selftest(int* failures) = 0;
+  virtual int phase_times(float* ms, int n) = 0;
 
   int cuda_fail(cudaError_t e, const char* where) {
     char buf[256];
@@ -112,45 +115,69 @@ struct Ctx final : kzg_gpu_ctx {
   uint64_t srs_n = 0;
   bool have_g2 = false;
   DevBuf g1, g2;             // Affine<Fp>[n], Affine<Fp2>[n]
-  DevBuf g1_table;           // precomputed window table (row 0 unused: g1 itself is row 0's content)
+  DevBuf g1_table, g2_table; // per-SRS window tables T[w][i] = 2^(c*w) * G_i (row 0 = the SRS itself)
   int table_c = 0, table_W = 0;
   // fixed-base tables of the generators
   DevBuf fb1, fb2;
   bool fb_ready = false;
   // scratch
-  DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, chunk_out, group_out, out_bytes,
-      out_inf, out_xyzz, poly0, poly1, qbytes, powers;
+  DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
+      out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, red0, red1, red2, red3;
   // description of the most recent launch, for fetch()
   uint64_t last_batch = 0;
   int last_group = 1;
 
   ~Ctx() override {
     cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first, &cursor,
-                      &sorted, &partial, &chunk_out, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
-                      &qbytes, &powers})
+    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first,
+                      &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
+                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &red0, &red1, &red2, &red3})
       b->release();
+    for (cudaEvent_t e : phase_ev) if (e) cudaEventDestroy(e);
     if (stream) cudaStreamDestroy(stream);
   }
 
   int init() {
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    for (cudaEvent_t& e : phase_ev) CK(cudaEventCreate(&e));
     return KZG_GPU_OK;
   }
 
   // ------------------------------------------------------------------ SRS
+  // window width of the per-SRS table: minimise  n*W*10 + 2^(c-1)*40  modmuls (mixed adds + bucket
+  // reduction) for an MSM over the whole SRS, subject to W <= MAXW and a table-size budget.
+  int pick_table_c(uint64_t n) const {
+    if (opt_window_bits) return opt_window_bits;
+    int best = 0;
+    double best_cost = 0;
+    for (int c = 7; c <= 21; c++) {
+      const int W = (C::SCALAR_BITS + 1 + c - 1) / c;
+      if (W > MAXW) continue;
+      if ((double)W * n * sizeof(Affine<Fp>) > 24e9) continue;
+      const double cost = (double)n * W * 10.0 + (double)(1ull << (c - 1)) * 40.0;
+      if (!best || cost < best_cost) { best = c; best_cost = cost; }
+    }
+    return best ? best : 8;
+  }
   int build_table() {
     g1_table.release();
+    g2_table.release();
     table_c = table_W = 0;
     if (!opt_precompute || srs_n == 0) return KZG_GPU_OK;
-    int c = opt_window_bits ? opt_window_bits : std::min(16, std::max(8, ilog2(srs_n) - 2));
-    int W = (C::SCALAR_BITS + 1 + c - 1) / c;
+    const int c = pick_table_c(srs_n);
+    const int W = (C::SCALAR_BITS + 1 + c - 1) / c;
     if (W > MAXW) return KZG_GPU_ERR_ARG;
     CK(g1_table.ensure((size_t)W * srs_n * sizeof(Affine<Fp>)));
     msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
         srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>());
     LAUNCHED();
+    if (have_g2 && opt_precompute >= 2) {
+      CK(g2_table.ensure((size_t)W * srs_n * sizeof(Affine<Fp2>)));
+      msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, stream>>>(
+          srs_n, srs_n, c, W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>());
+      LAUNCHED();
+    }
     CK(cudaStreamSynchronize(stream));
     table_c = c;
     table_W = W;
@@ -180,14 +207,49 @@ struct Ctx final : kzg_gpu_ctx {
   }
 
   // ------------------------------------------------------------------ MSM
+  // exclusive scan of counts (or of ceil(counts/chunk)) into out[0..n], three launches
+  int enqueue_scan(uint64_t n, int chunk, const uint32_t* in, uint32_t* out, uint32_t* zero_me) {
+    const uint64_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    CK(tile_sums.ensure((ntiles + 1) * 4));
+    scan_tile_sums<<<(unsigned)ntiles, SCAN_THREADS, 0, stream>>>(n, chunk, in, tile_sums.as<uint32_t>());
+    LAUNCHED();
+    scan_tiles<<<1, 1024, 0, stream>>>(ntiles, tile_sums.as<uint32_t>());
+    LAUNCHED();
+    scan_apply<<<(unsigned)ntiles, SCAN_THREADS, 0, stream>>>(n, chunk, in, tile_sums.as<uint32_t>(), out, zero_me);
+    LAUNCHED();
+    return KZG_GPU_OK;
+  }
+
+  // pairwise tree levels over two independent arrays (rows / columns side by side): every sum holds
+  // len[k] contiguous values; halves them until one value per sum is left.
+  template <class F>
+  int enqueue_pair_trees(XYZZ<F>*& in0, XYZZ<F>*& out0, uint64_t sums0, uint64_t len0, XYZZ<F>*& in1, XYZZ<F>*& out1,
+                         uint64_t sums1, uint64_t len1) {
+    while (len0 > 1 || len1 > 1) {
+      PairJob<F> j0{in0, out0, len0 > 1 ? sums0 * (len0 / 2) : 0};
+      PairJob<F> j1{in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0};
+      const uint64_t mx = std::max(j0.n_out, j1.n_out);
+      dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)148 * 64), 2);
+      msm_pair_sum<F><<<grid, 128, 0, stream>>>(j0, j1);
+      LAUNCHED();
+      if (len0 > 1) { std::swap(in0, out0); len0 /= 2; }
+      if (len1 > 1) { std::swap(in1, out1); len1 /= 2; }
+    }
+    return KZG_GPU_OK;
+  }
+
+  void phase_mark(int i) {
+    if (opt_profile && phase_ev[0]) cudaEventRecord(phase_ev[i], stream);
+  }
+
   // Enqueue one Pippenger pass for `batch` MSMs of `count` scalars (device-resident bytes).
   // Leaves affine bytes + flags in out_bytes/out_inf and the projective result of each MSM in out_xyzz.
   template <class F>
-  int enqueue_msm(const Affine<F>* bases, const Affine<F>* table, const uint8_t* d_scalars, uint64_t count,
+  int enqueue_msm(const Affine<F>* bases, const Affine<F>* table, int tc, const uint8_t* d_scalars, uint64_t count,
                   uint64_t batch, uint64_t base_offset) {
     MsmShape sh;
     const bool precomp = table != nullptr;
-    sh.c = precomp ? table_c : (opt_window_bits ? opt_window_bits : std::min(16, std::max(8, ilog2(count) - 4)));
+    sh.c = precomp ? tc : (opt_window_bits ? opt_window_bits : std::min(16, std::max(8, ilog2(count) - 4)));
     if (count < 32 && !precomp && !opt_window_bits) sh.c = 4;
     sh.W = (C::SCALAR_BITS + 1 + sh.c - 1) / sh.c;
     sh.nb = 1 << (sh.c - 1);
@@ -197,15 +259,17 @@ struct Ctx final : kzg_gpu_ctx {
     sh.batch = batch;
     sh.table_stride = srs_n;
     sh.base_offset = base_offset;
-    sh.chunk = opt_task_chunk ? opt_task_chunk : 64;
     const uint64_t records = count * batch * (uint64_t)sh.W;
+    // task length: long enough to amortise the fold, short enough that a small MSM still fills the machine
+    sh.chunk = opt_task_chunk ? std::min(opt_task_chunk, MSM_MAX_CHUNK)
+                              : (int)std::min<uint64_t>(48, std::max<uint64_t>(4, records / 65536));
     if (records >= (1ull << 31) || (precomp && (uint64_t)sh.W * srs_n >= (1ull << 31))) return KZG_GPU_ERR_ARG;
     const uint64_t nbuckets = sh.total_buckets();
     const uint64_t max_tasks = records / sh.chunk + nbuckets + 1;
-    int bpc = opt_reduce_chunk ? opt_reduce_chunk : 16;
-    bpc = std::min(bpc, sh.nb);
-    const int cpg = sh.nb / bpc;
     const uint64_t groups = sh.total_groups();
+    const int h = (sh.c - 1) / 2;
+    const uint64_t Cn = 1ull << h, R = (uint64_t)sh.nb / Cn;
+    const uint64_t red_cap = groups * ((uint64_t)sh.nb / 2 + R + Cn + 2);
 
     CK(digits.ensure(records * 4));
     CK(sorted.ensure(records * 4));
@@ -213,54 +277,101 @@ struct Ctx final : kzg_gpu_ctx {
     CK(starts.ensure((nbuckets + 1) * 4));
     CK(task_first.ensure((nbuckets + 1) * 4));
     CK(cursor.ensure((nbuckets + 1) * 4));
+    CK(hist.ensure((3 * (MSM_MAX_CHUNK + 1) + 1) * 4));
+    CK(slot_seg.ensure(max_tasks * sizeof(MsmSlotSeg)));
+    CK(tasks.ensure(max_tasks * sizeof(MsmTask)));
     CK(partial.ensure(max_tasks * sizeof(XYZZ<F>)));
-    CK(chunk_out.ensure(groups * cpg * sizeof(XYZZ<F>)));
+    for (DevBuf* rb : {&red0, &red1, &red2, &red3}) CK(rb->ensure(red_cap * sizeof(XYZZ<F>)));
     CK(group_out.ensure(groups * sizeof(XYZZ<F>)));
     CK(out_bytes.ensure(batch * (size_t)(4 * M)));
     CK(out_inf.ensure(batch * sizeof(int)));
     CK(out_xyzz.ensure(batch * sizeof(XYZZ<F>)));
+    uint32_t* d_hist = hist.as<uint32_t>();
+    uint32_t* d_hist_start = d_hist + (MSM_MAX_CHUNK + 2);  // [MSM_MAX_CHUNK + 1] = most tasks in one bucket
+    uint32_t* d_hist_cursor = d_hist_start + (MSM_MAX_CHUNK + 1);
 
     const int sms = 148;
+    phase_mark(0);
     CK(cudaMemsetAsync(counts.p, 0, (nbuckets + 1) * 4, stream));
+    CK(cudaMemsetAsync(hist.p, 0, (MSM_MAX_CHUNK + 2) * 4, stream));
     {
       const uint64_t total = count * batch;
       unsigned grid = (unsigned)std::min<uint64_t>((total + 255) / 256, (uint64_t)sms * 16);
       msm_digits<C><<<grid, 256, 0, stream>>>(sh, d_scalars, digits.as<int32_t>(), counts.as<uint32_t>());
       LAUNCHED();
     }
-    msm_scan<<<1, 1024, 0, stream>>>(nbuckets, sh.chunk, counts.as<uint32_t>(), starts.as<uint32_t>(),
-                                     task_first.as<uint32_t>(), cursor.as<uint32_t>());
-    LAUNCHED();
+    int rc = enqueue_scan(nbuckets, 0, counts.as<uint32_t>(), starts.as<uint32_t>(), cursor.as<uint32_t>());
+    if (rc) return rc;
     {
       unsigned grid = (unsigned)std::min<uint64_t>((records + 255) / 256, (uint64_t)sms * 32);
       msm_scatter<<<grid, 256, 0, stream>>>(sh, digits.as<int32_t>(), starts.as<uint32_t>(), cursor.as<uint32_t>(),
                                             sorted.as<uint32_t>());
       LAUNCHED();
     }
+    rc = enqueue_scan(nbuckets, sh.chunk, counts.as<uint32_t>(), task_first.as<uint32_t>(), nullptr);
+    if (rc) return rc;
     {
-      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 64);
-      msm_accumulate<F><<<grid, 128, 0, stream>>>(nbuckets, task_first.as<uint32_t>(), starts.as<uint32_t>(),
-                                                  sorted.as<uint32_t>(), precomp ? table : bases,
-                                                  partial.as<XYZZ<F>>());
+      unsigned grid = (unsigned)std::min<uint64_t>((nbuckets + 255) / 256, (uint64_t)sms * 8);
+      msm_task_hist<<<grid, 256, 0, stream>>>(nbuckets, sh.chunk, starts.as<uint32_t>(), task_first.as<uint32_t>(), d_hist);
+      LAUNCHED();
+      msm_task_hist_scan<<<1, 32, 0, stream>>>(d_hist, d_hist_start, d_hist_cursor);
+      LAUNCHED();
+      msm_task_place<<<grid, 256, 0, stream>>>(nbuckets, sh.chunk, starts.as<uint32_t>(), task_first.as<uint32_t>(),
+                                               d_hist_start, d_hist_cursor, tasks.as<MsmTask>(),
+                                               slot_seg.as<MsmSlotSeg>());
       LAUNCHED();
     }
+    phase_mark(1);
     {
-      const uint64_t total = groups * cpg;
-      unsigned grid = (unsigned)std::min<uint64_t>((total + 127) / 128, (uint64_t)sms * 64);
-      msm_reduce_chunks<F><<<grid, 128, 0, stream>>>(groups, sh.nb, bpc, task_first.as<uint32_t>(),
-                                                     partial.as<XYZZ<F>>(), chunk_out.as<XYZZ<F>>());
+      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)1 << 30);
+      msm_accumulate<F><<<grid, 128, 0, stream>>>(task_first.as<uint32_t>() + nbuckets, tasks.as<MsmTask>(),
+                                                  sorted.as<uint32_t>(), precomp ? table : bases, partial.as<XYZZ<F>>());
       LAUNCHED();
     }
+    phase_mark(2);
     {
-      constexpr int RT = 64;  // 64 * sizeof(XYZZ) = 12-24 KiB of shared memory
-      msm_reduce_groups<F, RT><<<(unsigned)groups, RT, RT * sizeof(XYZZ<F>), stream>>>(
-          cpg, chunk_out.as<XYZZ<F>>(), group_out.as<XYZZ<F>>());
-      LAUNCHED();
+      int levels = 0;
+      while ((1ull << levels) < max_tasks && levels < 31) levels++;  // bound on ceil(log2(max tasks in a bucket))
+      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 32);
+      for (int l = 0; l < levels; l++) {
+        msm_fold_level<F><<<grid, 128, 0, stream>>>(l, task_first.as<uint32_t>() + nbuckets, d_hist + MSM_MAX_CHUNK + 1,
+                                                    slot_seg.as<MsmSlotSeg>(), partial.as<XYZZ<F>>());
+        LAUNCHED();
+      }
     }
+    XYZZ<F>*rin = red0.as<XYZZ<F>>(), *rout = red1.as<XYZZ<F>>(), *cin = red2.as<XYZZ<F>>(), *cout = red3.as<XYZZ<F>>();
+    {
+      uint64_t Lr = Cn >= 2 ? Cn / 2 : 1, Lc = R >= 2 ? R / 2 : 1;
+      BucketJob<F> jr{rin, R, Cn, Cn, 1, groups * R * Lr};
+      BucketJob<F> jc{cin, Cn, R, 1, Cn, groups * Cn * Lc};
+      const uint64_t mx = std::max(jr.total, jc.total);
+      dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)sms * 64), 2);
+      msm_bucket_pairs<F><<<grid, 128, 0, stream>>>((uint64_t)sh.nb, task_first.as<uint32_t>(), partial.as<XYZZ<F>>(), jr, jc);
+      LAUNCHED();
+      rc = enqueue_pair_trees<F>(rin, rout, groups * R, Lr, cin, cout, groups * Cn, Lc);
+      if (rc) return rc;
+      // rin = row sums [groups * R], cin = column sums [groups * Cn]; weighted chunks, then trees again
+      const uint64_t Pr = R >= WCHUNK ? R / WCHUNK : 1, Pc = Cn >= WCHUNK ? Cn / WCHUNK : 1;
+      WeightedJob<F> wr{rin, rout, R, groups * Pr, 0u};
+      WeightedJob<F> wc{cin, cout, Cn, groups * Pc, 1u};
+      const uint64_t mw = std::max(wr.total, wc.total);
+      dim3 gridw((unsigned)std::min<uint64_t>((mw + 127) / 128, (uint64_t)sms * 64), 2);
+      msm_weighted_chunks<F><<<gridw, 128, 0, stream>>>(wr, wc);
+      LAUNCHED();
+      std::swap(rin, rout);
+      std::swap(cin, cout);
+      rc = enqueue_pair_trees<F>(rin, rout, groups, Pr, cin, cout, groups, Pc);
+      if (rc) return rc;
+    }
+    const XYZZ<F>*t1 = rin, *t2 = cin;
+    msm_group_combine<F><<<(unsigned)((groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
+    LAUNCHED();
+    phase_mark(3);
     msm_finish<F><<<(unsigned)((batch + 31) / 32), 32, 0, stream>>>(
         batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
         out_xyzz.as<XYZZ<F>>());
     LAUNCHED();
+    phase_mark(4);
     last_batch = batch;
     return KZG_GPU_OK;
   }
@@ -290,7 +401,7 @@ struct Ctx final : kzg_gpu_ctx {
       last_batch = 0;
       return KZG_GPU_OK;
     }
-    const bool use_table = group == 1 && g1_table.p != nullptr;
+    const bool use_table = group == 1 ? g1_table.p != nullptr : g2_table.p != nullptr;
     const int Wguess = use_table ? table_W : (C::SCALAR_BITS + 8) / 8;
     const uint64_t per_pass = do_fetch ? max_batch_per_pass(count, Wguess) : batch;
     for (uint64_t b0 = 0; b0 < batch; b0 += per_pass) {
@@ -305,10 +416,11 @@ struct Ctx final : kzg_gpu_ctx {
       }
       int rc;
       if (group == 1)
-        rc = enqueue_msm<Fp>(g1.as<Affine<Fp>>(), use_table ? g1_table.as<Affine<Fp>>() : nullptr, d_scal, count, nb,
-                             base_offset);
+        rc = enqueue_msm<Fp>(g1.as<Affine<Fp>>(), use_table ? g1_table.as<Affine<Fp>>() : nullptr, table_c, d_scal,
+                             count, nb, base_offset);
       else
-        rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), nullptr, d_scal, count, nb, base_offset);
+        rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), use_table ? g2_table.as<Affine<Fp2>>() : nullptr, table_c, d_scal,
+                              count, nb, base_offset);
       if (rc) return rc;
       if (do_fetch) {
         rc = fetch_locked(out ? out + b0 * (size_t)(nco * M) : nullptr, is_inf ? is_inf + b0 : nullptr);
@@ -497,6 +609,16 @@ struct Ctx final : kzg_gpu_ctx {
   }
 
   // ------------------------------------------------------------------ diagnostics
+  // CUDA-event durations of the last MSM pass ("profile" option): sort+tasks, accumulate, reduce, finish
+  int phase_times(float* ms, int n) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!ms || n < 4) return KZG_GPU_ERR_ARG;
+    if (!opt_profile) return KZG_GPU_ERR_STATE;
+    CK(cudaEventSynchronize(phase_ev[4]));
+    for (int i = 0; i < 4; i++) CK(cudaEventElapsedTime(&ms[i], phase_ev[i], phase_ev[i + 1]));
+    return KZG_GPU_OK;
+  }
   int microbench(int kind, double* ops) override {
     std::lock_guard<std::recursive_mutex> lock(mu);
     CK(cudaSetDevice(device));

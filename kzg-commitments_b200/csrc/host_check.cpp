@@ -79,21 +79,49 @@ int msm_host(uint64_t srs_n, const uint8_t* pts_bytes, const uint8_t* scalars, u
   }
   starts[nbuckets] = a; task_first[nbuckets] = b;
   for (uint64_t t = 0; t < records; t++) msm_scatter_thread(sh, digits.data(), starts.data(), cursor.data(), sorted.data(), t);
+  // tasks ordered by descending length (msm_task_hist / msm_task_place)
+  std::vector<uint32_t> hist(MSM_MAX_CHUNK + 2, 0), hist_start(MSM_MAX_CHUNK + 1), hcur(MSM_MAX_CHUNK + 1, 0);
+  for (uint64_t i = 0; i < nbuckets; i++) msm_task_hist_thread(chunk, starts.data(), task_first.data(), hist.data(), i);
+  uint32_t run = 0;
+  for (int i = 0; i <= MSM_MAX_CHUNK; i++) { hist_start[i] = run; run += hist[i]; }
+  if (run != b) return -2;
+  std::vector<MsmTask> tasks(b + 1);
+  std::vector<MsmSlotSeg> slot_seg(b + 1);
+  for (uint64_t i = 0; i < nbuckets; i++)
+    msm_task_place_thread(chunk, starts.data(), task_first.data(), hist_start.data(), hcur.data(), tasks.data(), slot_seg.data(), i);
+  for (uint32_t t = 1; t < b; t++) if (tasks[t].len > tasks[t - 1].len) return -3;
   std::vector<XYZZ<F>> partial(b + 1);
   for (uint32_t t = 0; t < b; t++)
-    msm_accumulate_thread<F>(nbuckets, task_first.data(), starts.data(), sorted.data(),
-                             precomp ? table.data() : bases.data(), partial.data(), t);
-  if (bpc > sh.nb) bpc = sh.nb;
-  const int cpg = sh.nb / bpc;
+    msm_accumulate_thread<F>(tasks.data(), sorted.data(), precomp ? table.data() : bases.data(), partial.data(), t);
+  for (uint64_t i = 0; i < nbuckets; i++) msm_fold_thread<F>(task_first.data(), partial.data(), i);
+  // 2-D bucket reduction (ctx.cuh::enqueue_msm with loops in place of launches)
+  (void)bpc;
   const uint64_t groups = sh.total_groups();
-  std::vector<XYZZ<F>> chunk_out(groups * cpg), group_out(groups);
-  for (uint64_t t = 0; t < groups * cpg; t++)
-    msm_reduce_chunk_thread<F>(sh.nb, bpc, task_first.data(), partial.data(), chunk_out.data(), t);
-  for (uint64_t g = 0; g < groups; g++) {
-    XYZZ<F> acc = XYZZ<F>::inf();
-    for (int j = 0; j < cpg; j++) acc.add(chunk_out[g * cpg + j]);
-    group_out[g] = acc;
-  }
+  const int h = (sh.c - 1) / 2;
+  const uint64_t Cn = 1ull << h, R = (uint64_t)sh.nb / Cn;
+  auto tree = [&](std::vector<XYZZ<F>> in, uint64_t sums, uint64_t len) {
+    while (len > 1) {
+      std::vector<XYZZ<F>> out(sums * (len / 2));
+      PairJob<F> jb{in.data(), out.data(), sums * (len / 2)};
+      for (uint64_t i = 0; i < jb.n_out; i++) msm_pair_sum_thread<F>(jb, i);
+      in.swap(out);
+      len /= 2;
+    }
+    return in;
+  };
+  const uint64_t Lr = Cn >= 2 ? Cn / 2 : 1, Lc = R >= 2 ? R / 2 : 1;
+  std::vector<XYZZ<F>> r0(groups * R * Lr), c0(groups * Cn * Lc);
+  BucketJob<F> jr{r0.data(), R, Cn, Cn, 1, groups * R * Lr}, jc{c0.data(), Cn, R, 1, Cn, groups * Cn * Lc};
+  for (uint64_t t = 0; t < jr.total; t++) msm_bucket_pair_thread<F>(jr, sh.nb, task_first.data(), partial.data(), t);
+  for (uint64_t t = 0; t < jc.total; t++) msm_bucket_pair_thread<F>(jc, sh.nb, task_first.data(), partial.data(), t);
+  std::vector<XYZZ<F>> rows = tree(r0, groups * R, Lr), cols = tree(c0, groups * Cn, Lc);
+  const uint64_t Pr = R >= WCHUNK ? R / WCHUNK : 1, Pc = Cn >= WCHUNK ? Cn / WCHUNK : 1;
+  std::vector<XYZZ<F>> wr(groups * Pr), wc(groups * Pc), group_out(groups);
+  WeightedJob<F> jwr{rows.data(), wr.data(), R, groups * Pr, 0u}, jwc{cols.data(), wc.data(), Cn, groups * Pc, 1u};
+  for (uint64_t t = 0; t < jwr.total; t++) msm_weighted_chunk_thread<F>(jwr, t);
+  for (uint64_t t = 0; t < jwc.total; t++) msm_weighted_chunk_thread<F>(jwc, t);
+  std::vector<XYZZ<F>> t1 = tree(wr, groups, Pr), t2 = tree(wc, groups, Pc);
+  for (uint64_t g = 0; g < groups; g++) msm_group_combine_thread<F>(h, t1.data(), t2.data(), group_out.data(), g);
   for (uint64_t m = 0; m < batch; m++)
     msm_finish_thread<F>(sh.groups_per_msm, sh.c, group_out.data(), out, is_inf, M, (XYZZ<F>*)nullptr, m);
   return 0;

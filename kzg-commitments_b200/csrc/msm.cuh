@@ -45,6 +45,13 @@ KZG_HD uint32_t atomic_inc_u32(uint32_t* p) {
   return (*p)++;
 #endif
 }
+KZG_HD void atomic_max_u32(uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  atomicMax(p, v);
+#else
+  if (v > *p) *p = v;
+#endif
+}
 KZG_HD int top_bit_u32(uint32_t v) {  // index of the highest set bit, v != 0
 #if defined(__CUDA_ARCH__)
   return 31 - __clz(v);
@@ -120,52 +127,93 @@ __global__ void msm_digits(MsmShape sh, const uint8_t* __restrict__ scalars, int
 }
 #endif
 
-// ---------------------------------------------------------------- 2. scans (one CTA, decoupled by thread ranges)
-// starts[b] = exclusive sum of counts; task_first[b] = exclusive sum of ceil(counts[b]/chunk).
-// starts[nbuckets] / task_first[nbuckets] hold the totals.  cursor[] is cleared for the scatter.
+// ---------------------------------------------------------------- 2. scans (multi-block)
+// Exclusive prefix sums over the bucket table in three launches: per-tile sums, one CTA scanning the
+// tile sums, per-tile rescan.  `chunk` != 0 scans ceil(x / chunk) instead of x (tasks per bucket).
+// out[n] receives the total.
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+KZG_HD uint32_t scan_value(uint32_t x, int chunk) { return chunk ? (x + (uint32_t)chunk - 1u) / (uint32_t)chunk : x; }
 #if defined(__CUDACC__)
-static __global__ void msm_scan(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ counts,
-                         uint32_t* __restrict__ starts, uint32_t* __restrict__ task_first,
-                         uint32_t* __restrict__ cursor) {
-  __shared__ uint32_t s_cnt[1024], s_tsk[1024];
-  const int T = blockDim.x, tid = threadIdx.x;
-  const uint64_t per = (nbuckets + T - 1) / T;
-  const uint64_t lo = min(per * tid, nbuckets), hi = min(lo + per, nbuckets);
-  uint32_t a = 0, b = 0;
-  for (uint64_t i = lo; i < hi; i++) {
-    uint32_t cnt = counts[i];
-    a += cnt;
-    b += (cnt + chunk - 1) / chunk;
+static __global__ void __launch_bounds__(SCAN_THREADS)
+scan_tile_sums(uint64_t n, int chunk, const uint32_t* __restrict__ in, uint32_t* __restrict__ tile_sums) {
+  __shared__ uint32_t sm[SCAN_THREADS / 32];
+  const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
+  uint32_t a = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    const uint64_t i = base + (uint64_t)k * SCAN_THREADS + threadIdx.x;
+    if (i < n) a += scan_value(in[i], chunk);
   }
-  s_cnt[tid] = a;
-  s_tsk[tid] = b;
+  for (int d = 16; d > 0; d >>= 1) a += __shfl_down_sync(0xffffffffu, a, d);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = a;
   __syncthreads();
-  if (tid == 0) {
-    uint32_t ra = 0, rb = 0;
-    for (int i = 0; i < T; i++) {
-      uint32_t ta = s_cnt[i], tb = s_tsk[i];
-      s_cnt[i] = ra; s_tsk[i] = rb;
-      ra += ta; rb += tb;
-    }
-    starts[nbuckets] = ra;
-    task_first[nbuckets] = rb;
-  }
-  __syncthreads();
-  a = s_cnt[tid];
-  b = s_tsk[tid];
-  for (uint64_t i = lo; i < hi; i++) {
-    uint32_t cnt = counts[i];
-    starts[i] = a;
-    task_first[i] = b;
-    cursor[i] = 0;
-    a += cnt;
-    b += (cnt + chunk - 1) / chunk;
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < SCAN_THREADS / 32; w++) t += sm[w];
+    tile_sums[blockIdx.x] = t;
   }
 }
+// one CTA: exclusive scan of tile_sums[0..ntiles) in place; total -> tile_sums[ntiles]
+static __global__ void __launch_bounds__(1024) scan_tiles(uint64_t ntiles, uint32_t* __restrict__ tile_sums) {
+  __shared__ uint32_t s_part[1024];
+  const int T = blockDim.x, tid = threadIdx.x;
+  const uint64_t per = (ntiles + T - 1) / T;
+  const uint64_t lo = min(per * (uint64_t)tid, ntiles), hi = min(lo + per, ntiles);
+  uint32_t a = 0;
+  for (uint64_t i = lo; i < hi; i++) a += tile_sums[i];
+  s_part[tid] = a;
+  __syncthreads();
+  for (int d = 1; d < T; d <<= 1) {  // Hillis-Steele inclusive scan of the per-thread sums
+    uint32_t v = tid >= d ? s_part[tid - d] : 0u;
+    __syncthreads();
+    s_part[tid] += v;
+    __syncthreads();
+  }
+  uint32_t run = s_part[tid] - a;  // exclusive prefix of this thread's range
+  for (uint64_t i = lo; i < hi; i++) {
+    const uint32_t v = tile_sums[i];
+    tile_sums[i] = run;
+    run += v;
+  }
+  if (tid == T - 1) tile_sums[ntiles] = s_part[T - 1];
+}
+static __global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply(uint64_t n, int chunk, const uint32_t* __restrict__ in, const uint32_t* __restrict__ tile_sums,
+           uint32_t* __restrict__ out, uint32_t* __restrict__ zero_me) {
+  __shared__ uint32_t sm[SCAN_THREADS];
+  // thread t owns SCAN_ITEMS consecutive elements of the tile
+  const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
+  uint32_t v[SCAN_ITEMS], a = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    v[k] = (base + k < n) ? scan_value(in[base + k], chunk) : 0u;
+    a += v[k];
+  }
+  sm[threadIdx.x] = a;
+  __syncthreads();
+  for (int d = 1; d < SCAN_THREADS; d <<= 1) {
+    uint32_t u = (int)threadIdx.x >= d ? sm[threadIdx.x - d] : 0u;
+    __syncthreads();
+    sm[threadIdx.x] += u;
+    __syncthreads();
+  }
+  uint32_t run = tile_sums[blockIdx.x] + sm[threadIdx.x] - a;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    if (base + k < n) {
+      out[base + k] = run;
+      if (zero_me) zero_me[base + k] = 0;
+    }
+    run += v[k];
+  }
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) out[n] = tile_sums[gridDim.x];
+}
+#endif
 
 // ---------------------------------------------------------------- 3. scatter (counting sort)
 // record = source index | sign << 31
-#endif
 KZG_HD void msm_scatter_thread(const MsmShape& sh, const int32_t* digits, const uint32_t* starts, uint32_t* cursor,
                                uint32_t* sorted, uint64_t t) {
   const int32_t d = digits[t];
@@ -190,102 +238,274 @@ static __global__ void msm_scatter(MsmShape sh, const int32_t* __restrict__ digi
 }
 #endif
 
-// ---------------------------------------------------------------- 4. bucket accumulation
-// One thread per task.  A task is a contiguous slice (<= chunk records) of ONE bucket's records;
-// the bucket owning task t is found by binary search in task_first[].
-template <class F>
-KZG_HD void msm_accumulate_thread(uint64_t nbuckets, const uint32_t* task_first, const uint32_t* starts,
-                                  const uint32_t* sorted, const Affine<F>* bases, XYZZ<F>* partial, uint32_t t) {
-  // largest b with task_first[b] <= t  (buckets with zero tasks share the value of their successor)
-  uint64_t lo = 0, hi = nbuckets;  // invariant: task_first[lo] <= t < task_first[hi]
-  while (hi - lo > 1) {
-    uint64_t mid = (lo + hi) >> 1;
-    if (task_first[mid] <= t) lo = mid; else hi = mid;
-  }
-  const uint64_t b = lo;
-  const uint32_t k = t - task_first[b];
+// ---------------------------------------------------------------- 4. tasks + bucket accumulation
+// A task is a contiguous slice (<= chunk records) of ONE bucket's sorted records; bucket b owns tasks
+// [task_first[b], task_first[b+1]) and its records are divided evenly among them.  Tasks are then
+// ordered by DESCENDING length (counting sort on the length) so that the 32 lanes of a warp run the
+// same trip count — bucket sizes are Poisson distributed and an unsorted assignment left 30 % of the
+// lanes idle (profiles/r1_accumulate_v1.md) — and so that the longest tasks start first.
+struct MsmTask {
+  uint32_t first;  // index of the first record in sorted[]
+  uint32_t len;    // number of records
+  uint32_t slot;   // where the partial sum goes: partial[slot], slot = task_first[b] + k
+};
+struct MsmSlotSeg {
+  uint32_t k, nt;  // partial[slot] is task k of a bucket with nt tasks (segment descriptor for the fold)
+};
+constexpr int MSM_MAX_CHUNK = 255;  // task-length histogram has MSM_MAX_CHUNK + 1 bins
+
+KZG_HD void msm_task_of_bucket(const uint32_t* starts, const uint32_t* task_first, uint64_t b, uint32_t k, MsmTask& t) {
   const uint32_t nt = task_first[b + 1] - task_first[b];
   const uint32_t s0 = starts[b], cnt = starts[b + 1] - s0;
   const uint32_t e0 = s0 + (uint32_t)(((uint64_t)k * cnt) / nt);
   const uint32_t e1 = s0 + (uint32_t)(((uint64_t)(k + 1) * cnt) / nt);
+  t.first = e0;
+  t.len = e1 - e0;
+  t.slot = task_first[b] + k;
+}
+// hist[chunk - len]++ for every task (bin 0 = longest)
+KZG_HD void msm_task_hist_thread(int chunk, const uint32_t* starts, const uint32_t* task_first, uint32_t* hist, uint64_t b) {
+  const uint32_t nt = task_first[b + 1] - task_first[b];
+  if (nt > hist[MSM_MAX_CHUNK + 1]) atomic_max_u32(&hist[MSM_MAX_CHUNK + 1], nt);  // extra bin: most tasks in one bucket
+  for (uint32_t k = 0; k < nt; k++) {
+    MsmTask t;
+    msm_task_of_bucket(starts, task_first, b, k, t);
+    atomic_inc_u32(&hist[chunk - (int)t.len]);
+  }
+}
+// tasks[hist_start[bin] + cursor[bin]++] = task
+KZG_HD void msm_task_place_thread(int chunk, const uint32_t* starts, const uint32_t* task_first, const uint32_t* hist_start,
+                                  uint32_t* cursor, MsmTask* tasks, MsmSlotSeg* slot_seg, uint64_t b) {
+  const uint32_t nt = task_first[b + 1] - task_first[b];
+  for (uint32_t k = 0; k < nt; k++) {
+    MsmTask t;
+    msm_task_of_bucket(starts, task_first, b, k, t);
+    const int bin = chunk - (int)t.len;
+    tasks[hist_start[bin] + atomic_inc_u32(&cursor[bin])] = t;
+    slot_seg[t.slot] = MsmSlotSeg{k, nt};
+  }
+}
+template <class F>
+KZG_HD void msm_accumulate_thread(const MsmTask* tasks, const uint32_t* sorted, const Affine<F>* bases,
+                                  XYZZ<F>* partial, uint32_t i) {
+  const MsmTask t = tasks[i];
   XYZZ<F> acc = XYZZ<F>::inf();
-  for (uint32_t e = e0; e < e1; e++) {
+  for (uint32_t e = t.first; e < t.first + t.len; e++) {
     const uint32_t rec = sorted[e];
     const Affine<F> p = bases[rec & 0x7fffffffu];
     acc.madd(p, (rec >> 31) != 0);
   }
-  partial[t] = acc;
+  partial[t.slot] = acc;
+}
+// Fold: partial[task_first[b]] = sum of bucket b's task partials, in place.  Afterwards the value of
+// bucket b is partial[task_first[b]] if it has any task and infinity otherwise (bucket_value()).
+// The device path (msm_fold_level) is a segmented binary tree; this per-thread body is the sequential
+// statement of the same sum, used by the host emulation.
+template <class F>
+KZG_HD void msm_fold_thread(const uint32_t* task_first, XYZZ<F>* partial, uint64_t b) {
+  const uint32_t t0 = task_first[b], t1 = task_first[b + 1];
+  if (t1 - t0 < 2) return;
+  XYZZ<F> acc = partial[t0];
+  for (uint32_t q = t0 + 1; q < t1; q++) acc.add(partial[q]);
+  partial[t0] = acc;
+}
+template <class F>
+KZG_HD XYZZ<F> bucket_value(const uint32_t* task_first, const XYZZ<F>* partial, uint64_t b) {
+  const uint32_t t0 = task_first[b];
+  if (task_first[b + 1] == t0) return XYZZ<F>::inf();
+  return partial[t0];
 }
 #if defined(__CUDACC__)
+// task-length histogram, privatised in shared memory
+static __global__ void __launch_bounds__(256)
+msm_task_hist(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts, const uint32_t* __restrict__ task_first,
+              uint32_t* __restrict__ hist) {
+  __shared__ uint32_t sh[MSM_MAX_CHUNK + 2];
+  for (int i = threadIdx.x; i <= MSM_MAX_CHUNK + 1; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  for (uint64_t b = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; b < nbuckets; b += (uint64_t)gridDim.x * blockDim.x)
+    msm_task_hist_thread(chunk, starts, task_first, sh, b);
+  __syncthreads();
+  for (int i = threadIdx.x; i <= MSM_MAX_CHUNK; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[i], sh[i]);
+  if (threadIdx.x == 0 && sh[MSM_MAX_CHUNK + 1]) atomicMax(&hist[MSM_MAX_CHUNK + 1], sh[MSM_MAX_CHUNK + 1]);
+}
+// hist (MSM_MAX_CHUNK+1 bins) -> exclusive starts; cursors cleared.  One warp is plenty.
+static __global__ void msm_task_hist_scan(const uint32_t* __restrict__ hist, uint32_t* __restrict__ hist_start,
+                                          uint32_t* __restrict__ cursor) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  uint32_t run = 0;
+  for (int i = 0; i <= MSM_MAX_CHUNK; i++) {
+    hist_start[i] = run;
+    run += hist[i];
+    cursor[i] = 0;
+  }
+}
+// placement: a CTA first counts its tasks per bin in shared memory, reserves one range per bin with a
+// single global atomic, then its threads take slots inside the reserved ranges.
+static __global__ void __launch_bounds__(256)
+msm_task_place(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts, const uint32_t* __restrict__ task_first,
+               const uint32_t* __restrict__ hist_start, uint32_t* __restrict__ cursor, MsmTask* __restrict__ tasks,
+               MsmSlotSeg* __restrict__ slot_seg) {
+  __shared__ uint32_t cnt[MSM_MAX_CHUNK + 2], base[MSM_MAX_CHUNK + 1];
+  for (uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x; b0 < nbuckets; b0 += (uint64_t)gridDim.x * blockDim.x) {
+    for (int i = threadIdx.x; i <= MSM_MAX_CHUNK + 1; i += blockDim.x) cnt[i] = 0;
+    __syncthreads();
+    const uint64_t b = b0 + threadIdx.x;
+    if (b < nbuckets) msm_task_hist_thread(chunk, starts, task_first, cnt, b);
+    __syncthreads();
+    for (int i = threadIdx.x; i <= MSM_MAX_CHUNK; i += blockDim.x) {
+      base[i] = cnt[i] ? hist_start[i] + atomicAdd(&cursor[i], cnt[i]) : 0u;
+      cnt[i] = 0;
+    }
+    __syncthreads();
+    if (b < nbuckets) msm_task_place_thread(chunk, starts, task_first, base, cnt, tasks, slot_seg, b);
+    __syncthreads();
+  }
+}
 template <class F>
 __global__ void __launch_bounds__(128)
-msm_accumulate(uint64_t nbuckets, const uint32_t* __restrict__ task_first, const uint32_t* __restrict__ starts,
-               const uint32_t* __restrict__ sorted, const Affine<F>* __restrict__ bases,
-               XYZZ<F>* __restrict__ partial) {
-  const uint32_t ntasks = task_first[nbuckets];
-  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < ntasks; t += gridDim.x * blockDim.x)
-    msm_accumulate_thread<F>(nbuckets, task_first, starts, sorted, bases, partial, t);
+msm_accumulate(const uint32_t* __restrict__ ntasks_ptr, const MsmTask* __restrict__ tasks,
+               const uint32_t* __restrict__ sorted, const Affine<F>* __restrict__ bases, XYZZ<F>* __restrict__ partial) {
+  const uint32_t ntasks = *ntasks_ptr;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ntasks; i += gridDim.x * blockDim.x)
+    msm_accumulate_thread<F>(tasks, sorted, bases, partial, i);
+}
+// Device fold: a segmented binary tree over the flat array of task partials, one launch per level.
+// At level l the partial of task k (k a multiple of 2^(l+1)) absorbs that of task k + 2^l of the same
+// bucket, so a bucket with nt tasks is folded in ceil(log2 nt) single additions instead of nt - 1
+// sequential ones (a sequential XYZZ addition chain runs at ~19 us per link; with structured scalars
+// or a short top window a few buckets own hundreds of tasks).  Levels beyond the largest task count
+// (max_nt, found by msm_task_hist) return immediately.
+template <class F>
+__global__ void __launch_bounds__(128)
+msm_fold_level(int level, const uint32_t* __restrict__ ntasks_ptr, const uint32_t* __restrict__ max_nt,
+               const MsmSlotSeg* __restrict__ slot_seg, XYZZ<F>* __restrict__ partial) {
+  const uint32_t stride = 1u << level;
+  if (stride >= *max_nt) return;
+  const uint32_t ntasks = *ntasks_ptr;
+  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < ntasks; q += gridDim.x * blockDim.x) {
+    const MsmSlotSeg sg = slot_seg[q];
+    if ((sg.k & (2u * stride - 1u)) == 0u && sg.k + stride < sg.nt) partial[q].add(partial[q + stride]);
+  }
 }
 #endif
 
 // ---------------------------------------------------------------- 5. bucket reduction
-// chunk_out[group * chunks_per_group + j] = sum over buckets b in chunk j of (b+1) * B_b,
-// B_b = sum of the bucket's task partials.  Running sums from the top of the chunk give
-// sum (b-lo+1) B_b; the remaining lo * S is one short double-and-add.
+// Per group of nb = R * Cn buckets (Cn = 2^h):  sum_b (b+1) B_b  with b = hi*Cn + lo  equals
+//     Cn * sum_hi hi * row[hi]  +  sum_lo (lo+1) * col[lo],
+// row[hi] = sum_lo B[hi][lo], col[lo] = sum_hi B[hi][lo].  Every step below is a single group
+// operation per thread, because one thread's XYZZ addition is a ~19 us dependent carry chain
+// (profiles/r1b): the 2*nb unweighted additions of the row/column sums are BINARY trees (one launch
+// per level, rows and columns side by side in blockIdx.y), and the two short weighted sums run in
+// chunks of WCHUNK terms (running sums + a double-and-add correction for the chunk offset) followed
+// by the same pairwise trees.  All lengths are powers of two.
+constexpr int WCHUNK = 4;  // terms per thread of the weighted sums
+
+// level 0 of a row/column tree, reading bucket values through task_first:
+// out[(g*nsums + s)*P + p] = B[g*nb + s*sstride + 2p*jstride] + B[.. + (2p+1)*jstride],  P = max(len/2, 1)
 template <class F>
-KZG_HD void msm_reduce_chunk_thread(int nb, int buckets_per_chunk, const uint32_t* task_first,
-                                    const XYZZ<F>* partial, XYZZ<F>* chunk_out, uint64_t t) {
-  const int cpg = nb / buckets_per_chunk;
-  const uint64_t g = t / cpg;
-  const uint32_t j = (uint32_t)(t - g * cpg);
-  const uint32_t lo = j * buckets_per_chunk;
+struct BucketJob {
+  XYZZ<F>* out;
+  uint64_t nsums, len, sstride, jstride, total;  // total = groups * nsums * P
+};
+template <class F>
+KZG_HD void msm_bucket_pair_thread(const BucketJob<F>& jb, uint64_t nb, const uint32_t* task_first, const XYZZ<F>* partial,
+                                   uint64_t t) {
+  const uint64_t P = jb.len >= 2 ? jb.len / 2 : 1;
+  const uint64_t p = t % P, gs = t / P;
+  const uint64_t s = gs % jb.nsums, g = gs / jb.nsums;
+  const uint64_t b0 = g * nb + s * jb.sstride + 2 * p * jb.jstride;
+  XYZZ<F> acc = bucket_value<F>(task_first, partial, b0);
+  if (jb.len >= 2) acc.add(bucket_value<F>(task_first, partial, b0 + jb.jstride));
+  jb.out[t] = acc;
+}
+// further levels: out[i] = in[2i] + in[2i+1]
+template <class F>
+struct PairJob {
+  const XYZZ<F>* in;
+  XYZZ<F>* out;
+  uint64_t n_out;
+};
+template <class F>
+KZG_HD void msm_pair_sum_thread(const PairJob<F>& jb, uint64_t i) {
+  XYZZ<F> acc = jb.in[2 * i];
+  acc.add(jb.in[2 * i + 1]);
+  jb.out[i] = acc;
+}
+// k * P for a small non-negative k (chunk offsets of the weighted sums)
+template <class F>
+KZG_HD XYZZ<F> small_mul(const XYZZ<F>& p, uint32_t k) {
+  XYZZ<F> m = XYZZ<F>::inf();
+  if (k == 0 || p.is_inf()) return m;
+  for (int bit = top_bit_u32(k); bit >= 0; bit--) {
+    m.dbl();
+    if ((k >> bit) & 1) m.add(p);
+  }
+  return m;
+}
+// out[g*P + p] = sum_{j in chunk p} (j + woff) * in[g*m + j],  chunk p = [p*WCHUNK, ...), P = max(m/WCHUNK, 1)
+template <class F>
+struct WeightedJob {
+  const XYZZ<F>* in;
+  XYZZ<F>* out;
+  uint64_t m, total;  // total = groups * P
+  uint32_t woff;
+};
+template <class F>
+KZG_HD void msm_weighted_chunk_thread(const WeightedJob<F>& jb, uint64_t t) {
+  const uint64_t m = jb.m;
+  const uint64_t P = m >= WCHUNK ? m / WCHUNK : 1;
+  const uint64_t p = t % P, g = t / P;
+  const uint64_t j0 = p * WCHUNK, j1 = (j0 + WCHUNK < m) ? j0 + WCHUNK : m;
   XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
-  for (int b = buckets_per_chunk - 1; b >= 0; b--) {
-    const uint64_t key = g * nb + lo + b;
-    const uint32_t t0 = task_first[key], t1 = task_first[key + 1];
-    for (uint32_t q = t0; q < t1; q++) run.add(partial[q]);
+  for (uint64_t j = j1; j > j0; j--) {  // acc = sum (j - j0 + 1) * in[j]
+    run.add(jb.in[g * m + j - 1]);
     acc.add(run);
   }
-  if (lo != 0 && !run.is_inf()) {
-    XYZZ<F> m = XYZZ<F>::inf();
-    for (int bit = top_bit_u32(lo); bit >= 0; bit--) {
-      m.dbl();
-      if ((lo >> bit) & 1) m.add(run);
-    }
-    acc.add(m);
+  const uint32_t k = (uint32_t)j0 + jb.woff;  // weights wanted: j + woff = (j - j0 + 1) + (j0 + woff - 1)
+  if (k >= 1) acc.add(small_mul<F>(run, k - 1));
+  else {       // k == 0 (rows, first chunk): weights j - j0, i.e. one `run` too many
+    run.negate();
+    acc.add(run);
   }
-  chunk_out[t] = acc;
+  jb.out[t] = acc;
+}
+// group_out[g] = 2^h * T1[g] + T2[g]
+template <class F>
+KZG_HD void msm_group_combine_thread(int h, const XYZZ<F>* t1, const XYZZ<F>* t2, XYZZ<F>* group_out, uint64_t g) {
+  XYZZ<F> acc = t1[g];
+  for (int k = 0; k < h; k++) acc.dbl();
+  acc.add(t2[g]);
+  group_out[g] = acc;
 }
 #if defined(__CUDACC__)
 template <class F>
 __global__ void __launch_bounds__(128)
-msm_reduce_chunks(uint64_t total_groups, int nb, int buckets_per_chunk, const uint32_t* __restrict__ task_first,
-                  const XYZZ<F>* __restrict__ partial, XYZZ<F>* __restrict__ chunk_out) {
-  const uint64_t total = total_groups * (uint64_t)(nb / buckets_per_chunk);
-  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total;
-       t += (uint64_t)gridDim.x * blockDim.x)
-    msm_reduce_chunk_thread<F>(nb, buckets_per_chunk, task_first, partial, chunk_out, t);
+msm_bucket_pairs(uint64_t nb, const uint32_t* __restrict__ task_first, const XYZZ<F>* __restrict__ partial,
+                 BucketJob<F> j0, BucketJob<F> j1) {
+  const BucketJob<F>& jb = blockIdx.y ? j1 : j0;
+  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < jb.total; t += (uint64_t)gridDim.x * blockDim.x)
+    msm_bucket_pair_thread<F>(jb, nb, task_first, partial, t);
 }
-
-// group_out[g] = sum of the group's chunk results.  One CTA per group, tree in shared memory.
-template <class F, int THREADS>
-__global__ void __launch_bounds__(THREADS)
-msm_reduce_groups(int cpg, const XYZZ<F>* __restrict__ chunk_out, XYZZ<F>* __restrict__ group_out) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  XYZZ<F>* sm = reinterpret_cast<XYZZ<F>*>(smem_raw);
-  const uint64_t g = blockIdx.x;
-  XYZZ<F> acc = XYZZ<F>::inf();
-  for (int j = threadIdx.x; j < cpg; j += THREADS) acc.add(chunk_out[g * cpg + j]);
-  sm[threadIdx.x] = acc;
-  __syncthreads();
-  for (int s = THREADS / 2; s > 0; s >>= 1) {
-    if ((int)threadIdx.x < s) {
-      acc.add(sm[threadIdx.x + s]);
-      sm[threadIdx.x] = acc;
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) group_out[g] = acc;
+template <class F>
+__global__ void __launch_bounds__(128) msm_pair_sum(PairJob<F> j0, PairJob<F> j1) {
+  const PairJob<F>& jb = blockIdx.y ? j1 : j0;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < jb.n_out; i += (uint64_t)gridDim.x * blockDim.x)
+    msm_pair_sum_thread<F>(jb, i);
+}
+template <class F>
+__global__ void __launch_bounds__(128) msm_weighted_chunks(WeightedJob<F> j0, WeightedJob<F> j1) {
+  const WeightedJob<F>& jb = blockIdx.y ? j1 : j0;
+  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < jb.total; t += (uint64_t)gridDim.x * blockDim.x)
+    msm_weighted_chunk_thread<F>(jb, t);
+}
+template <class F>
+__global__ void __launch_bounds__(128)
+msm_group_combine(uint64_t groups, int h, const XYZZ<F>* __restrict__ t1, const XYZZ<F>* __restrict__ t2,
+                  XYZZ<F>* __restrict__ group_out) {
+  const uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (g < groups) msm_group_combine_thread<F>(h, t1, t2, group_out, g);
 }
 #endif
 

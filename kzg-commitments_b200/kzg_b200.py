@@ -70,6 +70,7 @@ def load_library():
         "kzg_gpu_launch_count": (u64, [vp]),
         "kzg_gpu_microbench": (ctypes.c_int, [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
         "kzg_gpu_selftest": (ctypes.c_int, [vp, ip]),
+        "kzg_gpu_phase_times": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_float), ctypes.c_int]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)  # AttributeError if the library does not export the declared symbol
@@ -85,6 +86,7 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_msm_g2", "kzg_gpu_msm_g1_batch", "kzg_gpu_msm_g1_launch", "kzg_gpu_msm_fetch",
     "kzg_gpu_msm_fetch_partial", "kzg_gpu_g1_sum_partials", "kzg_gpu_poly_quotient", "kzg_gpu_poly_eval_range",
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
+    "kzg_gpu_phase_times",
 ]
 
 
@@ -232,6 +234,14 @@ class Context:
         v = ctypes.c_double(0)
         self._check(self.lib.kzg_gpu_microbench(self.h, kind, ctypes.byref(v)), "microbench")
         return v.value
+
+    def phase_times(self):
+        """ms of the last MSM pass: {sort, accumulate, reduce, finish} (needs set_option("profile", 1))."""
+        ms = (ctypes.c_float * 4)()
+        rc = self.lib.kzg_gpu_phase_times(self.h, ms, 4)
+        if rc != 0:
+            return None
+        return dict(zip(("sort", "accumulate", "reduce", "finish"), [float(v) for v in ms]))
 
     def selftest(self):
         f = ctypes.c_int(-1)

@@ -40,6 +40,7 @@ def main():
     print(json.dumps(res["microbench"]), flush=True)
     stream = torch.cuda.ExternalStream(ctx.stream)
     ctx.set_option("setup_g2", 0)
+    ctx.set_option("profile", 1)
     for lg in [int(x) for x in args.sizes.split(",")]:
         n = 1 << lg
         sc = torch.from_numpy(random_scalars(n, lg).view(np.uint8).reshape(-1)).cuda()
@@ -63,7 +64,7 @@ def main():
                     xy, inf = ctx.msm_fetch(1)
                     row = {"log2n": lg, "precompute": pre, "window_bits": wb, "task_chunk": ch, "ms": min(times[1:]),
                            "first_ms": times[0], "mpts_per_s": n / min(times[1:]) / 1e3, "setup_s": t_setup,
-                           "xy": xy[:8].hex()}
+                           "xy": xy[:8].hex(), "phases": ctx.phase_times()}
                     res["msm"].append(row)
                     print(json.dumps(row), flush=True)
     if args.out:
