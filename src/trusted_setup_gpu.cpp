@@ -1,0 +1,338 @@
+// src/trusted_setup_gpu.cpp — drop-in replacement for the reference's src/trusted_setup.cpp.
+//
+// Compiled against the reference's UNMODIFIED headers (src/kzg.h, src/util.h, config/curve_*/kzg_config.h)
+// and linked with the reference's unmodified blob/poly/commit/proof/util translation units, so every caller
+// of kzg.h (benchmark/benchmark.cpp, testing/testing.cpp, demo/shared/kzg-cli.cpp) builds and runs unchanged.
+// What changes is below the private methods (reference file:line in brackets):
+//   polyeval_G1  [src/trusted_setup.cpp:149-174]   -> kzg_gpu_msm_g1      (Pippenger MSM on the B200)
+//   polyeval_G2  [src/trusted_setup.cpp:176-201]   -> kzg_gpu_msm_g2
+//   create_proof [src/trusted_setup.cpp:214-228]   -> kzg_gpu_prove       (quotient + MSM chained on device;
+//                                                     (P - I)/Z == P div Z, so neither I nor the evaluations are needed)
+//   trusted_setup(int) [src/trusted_setup.cpp:21-74, 123-135] -> kzg_gpu_setup_powers (fixed-base batch)
+// What does not change: argument checks and exception types/messages, the SRS file format, the host-side
+// interpolation of verify_proof (util.cpp linear_roots_and_polyfit) and the two pairings
+// (PAIR_ate / PAIR_fexp, src/trusted_setup.cpp:242-253), which stay MIRACL host code by design.
+// There is no CPU fallback: a failing C-ABI call (no GPU, out of memory) throws std::runtime_error.
+//
+// kzg.h gives trusted_setup no spare member and no destructor, so the device context of a setup lives in
+// a side table keyed by the object's address and validated by a fingerprint of its SRS.
+#include <kzg.h>
+
+#include <cstdint>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <map>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "util.h"
+#include "../include/kzg_gpu.h"
+
+int kzg::CURVE_ORDER_BYTES;
+
+namespace {
+
+constexpr int M = MODBYTES_CURVE;
+constexpr int G1_BYTES = 2 * M;   // x | y
+constexpr int G2_BYTES = 4 * M;   // x.b | x.a | y.b | y.a
+constexpr int CURVE_ID = (M == 20) ? KZG_GPU_BN158 : (M == 32) ? KZG_GPU_BN254 : KZG_GPU_BLS12381;
+
+[[noreturn]] void fail(const kzg_gpu_ctx* ctx, int rc, const char* what) {
+  std::string msg = std::string("kzg gpu: ") + what + ": " + kzg_gpu_strerror(rc);
+  if (ctx && *kzg_gpu_last_error(ctx)) msg += std::string(" [") + kzg_gpu_last_error(ctx) + "]";
+  throw std::runtime_error(msg);
+}
+
+// affine big-endian coordinates of a point, i.e. the octet body after the 0x04 tag
+void g1_body(ECP& p, uint8_t* out) {
+  char buf[G1_BYTES + 1];
+  octet o = {0, (int)sizeof(buf), buf};
+  ECP_toOctet(&o, &p, false);          // normalises p in place; infinity leaves zeros
+  if (ECP_isinf(&p)) memset(out, 0, G1_BYTES); else memcpy(out, buf + 1, G1_BYTES);
+}
+void g2_body(ECP2& p, uint8_t* out) {
+  char buf[G2_BYTES + 1];
+  octet o = {0, (int)sizeof(buf), buf};
+  ECP2_toOctet(&o, &p, false);
+  if (ECP2_isinf(&p)) memset(out, 0, G2_BYTES); else memcpy(out, buf + 1, G2_BYTES);
+}
+ECP g1_from_body(const uint8_t* xy, int is_inf) {
+  ECP p;
+  if (is_inf) { ECP_inf(&p); return p; }
+  char buf[G1_BYTES + 1];
+  buf[0] = 0x04;
+  memcpy(buf + 1, xy, G1_BYTES);
+  octet o = {G1_BYTES + 1, (int)sizeof(buf), buf};
+  if (!ECP_fromOctet(&p, &o)) throw std::runtime_error("kzg gpu: device returned a point that is not on the curve");
+  return p;
+}
+ECP2 g2_from_body(const uint8_t* xy, int is_inf) {
+  ECP2 p;
+  if (is_inf) { ECP2_inf(&p); return p; }
+  char buf[G2_BYTES + 1];
+  buf[0] = 0x04;
+  memcpy(buf + 1, xy, G2_BYTES);
+  octet o = {G2_BYTES + 1, (int)sizeof(buf), buf};
+  if (!ECP2_fromOctet(&p, &o)) throw std::runtime_error("kzg gpu: device returned a G2 point that is not on the curve");
+  return p;
+}
+
+// coefficients of P as flat little-endian CURVE_ORDER_BYTES records (what BIG_from_ZZ starts from, util.cpp:31-43)
+std::vector<uint8_t> pack_coeffs(const ZZ_pX& P) {
+  const long n = deg(P) + 1;
+  const int SB = kzg::CURVE_ORDER_BYTES;
+  std::vector<uint8_t> raw((size_t)n * SB);
+  for (long i = 0; i < n; i++) BytesFromZZ(raw.data() + (size_t)i * SB, rep(P[i]), SB);
+  return raw;
+}
+
+// ---- side table: trusted_setup object -> device context with its SRS resident
+struct DeviceSide {
+  kzg_gpu_ctx* ctx = nullptr;
+  size_t n = 0;
+  std::vector<uint8_t> stamp;  // first and last G1 point
+  uint64_t age = 0;
+};
+std::mutex g_mu;
+std::map<const void*, DeviceSide> g_sides;
+uint64_t g_clock = 0;
+
+std::vector<uint8_t> stamp_of(std::vector<ECP>& g1) {
+  std::vector<uint8_t> s(2 * G1_BYTES);
+  g1_body(g1.front(), s.data());
+  g1_body(g1.back(), s.data() + G1_BYTES);
+  return s;
+}
+void evict_old_locked() {
+  while (g_sides.size() > 4) {
+    auto oldest = g_sides.begin();
+    for (auto it = g_sides.begin(); it != g_sides.end(); ++it)
+      if (it->second.age < oldest->second.age) oldest = it;
+    kzg_gpu_ctx_destroy(oldest->second.ctx);
+    g_sides.erase(oldest);
+  }
+}
+kzg_gpu_ctx* new_ctx() {
+  kzg_gpu_ctx* ctx = nullptr;
+  int rc = kzg_gpu_ctx_create(&ctx, CURVE_ID, 0);
+  if (rc) fail(nullptr, rc, "kzg_gpu_ctx_create (a CUDA device is required; there is no CPU fallback)");
+  return ctx;
+}
+void remember(const void* self, kzg_gpu_ctx* ctx, std::vector<ECP>& g1) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  auto it = g_sides.find(self);
+  if (it != g_sides.end()) kzg_gpu_ctx_destroy(it->second.ctx);
+  DeviceSide& d = g_sides[self];
+  d.ctx = ctx;
+  d.n = g1.size();
+  d.stamp = stamp_of(g1);
+  d.age = ++g_clock;
+  evict_old_locked();
+}
+// context of `self`, uploading the SRS the first time (or again if the object at this address changed)
+kzg_gpu_ctx* device_of(const void* self, std::vector<ECP>& g1, std::vector<ECP2>& g2) {
+  if (g1.empty()) throw std::runtime_error("kzg gpu: empty trusted setup");
+  {
+    std::lock_guard<std::mutex> lock(g_mu);
+    auto it = g_sides.find(self);
+    if (it != g_sides.end() && it->second.n == g1.size() && it->second.stamp == stamp_of(g1)) {
+      it->second.age = ++g_clock;
+      return it->second.ctx;
+    }
+  }
+  const size_t n = g1.size();
+  std::vector<uint8_t> b1(n * (size_t)G1_BYTES), b2(g2.size() == n ? n * (size_t)G2_BYTES : 0);
+  for (size_t i = 0; i < n; i++) g1_body(g1[i], b1.data() + i * G1_BYTES);
+  for (size_t i = 0; i < n && !b2.empty(); i++) g2_body(g2[i], b2.data() + i * G2_BYTES);
+  kzg_gpu_ctx* ctx = new_ctx();
+  int rc = kzg_gpu_srs_load(ctx, n, b1.data(), b2.empty() ? nullptr : b2.data());
+  if (rc) { std::string e = kzg_gpu_last_error(ctx); kzg_gpu_ctx_destroy(ctx); throw std::runtime_error("kzg gpu: srs_load failed " + e); }
+  remember(self, ctx, g1);
+  return ctx;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+void kzg::init() {  // same contract as the reference: NTL modulus = group order, CURVE_ORDER_BYTES = its byte length
+  ZZ order = ZZ_from_BIG(CURVE_Order);
+  ZZ_p::init(order);
+  kzg::CURVE_ORDER_BYTES = NumBytes(order);
+}
+
+// trusted_setup(int): the secret is drawn exactly as the reference does (generate_random_BIG, util.cpp:62-76);
+// the n powers and the 2n fixed-base multiplications run on the device, which keeps the SRS resident.
+kzg::trusted_setup::trusted_setup(int num_coeff) {
+  if (num_coeff < 2) throw invalid_argument("num_coeff must be at least 2");
+  if (kzg::CURVE_ORDER_BYTES == 0) kzg::init();
+  BIG secret;
+  generate_random_BIG(secret);
+  const int SB = kzg::CURVE_ORDER_BYTES;
+  std::vector<uint8_t> s_le(SB);
+  BytesFromZZ(s_le.data(), ZZ_from_BIG(secret), SB);
+
+  const size_t n = (size_t)num_coeff;
+  std::vector<uint8_t> b1(n * G1_BYTES), b2(n * G2_BYTES);
+  kzg_gpu_ctx* ctx = new_ctx();
+  int rc = kzg_gpu_setup_powers(ctx, s_le.data(), n, b1.data(), b2.data());
+  memset(s_le.data(), 0, s_le.size());
+  if (rc) { std::string e = kzg_gpu_last_error(ctx); kzg_gpu_ctx_destroy(ctx); throw std::runtime_error("kzg gpu: setup_powers failed " + e); }
+  _G1.resize(n);
+  _G2.resize(n);
+  for (size_t i = 0; i < n; i++) {
+    _G1[i] = g1_from_body(b1.data() + i * G1_BYTES, 0);
+    _G2[i] = g2_from_body(b2.data() + i * G2_BYTES, 0);
+  }
+  remember(this, ctx, _G1);
+}
+
+// trusted_setup(filename): same file format and the same three failure modes as src/trusted_setup.cpp:76-121.
+kzg::trusted_setup::trusted_setup(const std::string& filename) {
+  kzg::init();
+  std::ifstream file(filename, std::ios::in | std::ios::binary);
+  if (!file.is_open()) throw runtime_error("could not open trusted setup file");
+  std::vector<char> raw((std::istreambuf_iterator<char>(file)), std::istreambuf_iterator<char>());
+  size_t pos = 0;
+  auto take = [&](void* dst, size_t len) {
+    if (pos + len > raw.size()) return false;
+    memcpy(dst, raw.data() + pos, len);
+    pos += len;
+    return true;
+  };
+  uint64_t n = 0;
+  if (!take(&n, sizeof n)) throw runtime_error("bad trusted setup file");
+  _G1.reserve((size_t)n);
+  _G2.reserve((size_t)n);
+  for (int group = 1; group <= 2; group++) {
+    const size_t cap = (group == 1 ? G1_BYTES : G2_BYTES) + 1;
+    for (uint64_t i = 0; i < n; i++) {
+      uint32_t len = 0;
+      char body[G2_BYTES + 1];
+      bool ok = take(&len, sizeof len) && len <= cap && take(body, len);
+      octet o = {(int)len, (int)cap, body};
+      if (group == 1) {
+        ECP p;
+        if (!ok || !ECP_fromOctet(&p, &o)) throw runtime_error("bad trusted setup file");
+        _G1.push_back(p);
+      } else {
+        ECP2 p;
+        if (!ok || !ECP2_fromOctet(&p, &o)) throw logic_error("bad trusted setup file");
+        _G2.push_back(p);
+      }
+    }
+  }
+}
+
+// Declared private in kzg.h; the reference's thread fan-out over index ranges is replaced by one device
+// batch in the constructor above, so nothing calls this any more.
+void kzg::trusted_setup::generate_elements_range(int, int, const std::vector<BIG>&) {
+  throw logic_error("generate_elements_range is not used by the GPU trusted setup");
+}
+
+ECP kzg::trusted_setup::polyeval_G1(const ZZ_pX& P) {
+  if (deg(P) == -1) return g1_from_body(nullptr, 1);
+  kzg_gpu_ctx* ctx = device_of(this, _G1, _G2);
+  std::vector<uint8_t> raw = pack_coeffs(P);
+  uint8_t xy[G1_BYTES];
+  int is_inf = 0;
+  int rc = kzg_gpu_msm_g1(ctx, raw.data(), (uint64_t)(deg(P) + 1), 0, xy, &is_inf);
+  if (rc) fail(ctx, rc, "msm_g1");
+  return g1_from_body(xy, is_inf);
+}
+
+ECP2 kzg::trusted_setup::polyeval_G2(const ZZ_pX& P) {
+  if (deg(P) == -1) return g2_from_body(nullptr, 1);
+  kzg_gpu_ctx* ctx = device_of(this, _G1, _G2);
+  std::vector<uint8_t> raw = pack_coeffs(P);
+  uint8_t xy[G2_BYTES];
+  int is_inf = 0;
+  int rc = kzg_gpu_msm_g2(ctx, raw.data(), (uint64_t)(deg(P) + 1), 0, xy, &is_inf);
+  if (rc) fail(ctx, rc, "msm_g2");
+  return g2_from_body(xy, is_inf);
+}
+
+kzg::commit kzg::trusted_setup::create_commit(const kzg::poly& poly) {
+  if (deg(poly.get_poly()) + 1 >= (long)_G1.size())
+    throw invalid_argument("polynomial degree be at most one less than the setup size (num_coeffs)");
+  return kzg::commit(polyeval_G1(poly.get_poly()));
+}
+
+bool kzg::trusted_setup::verify_commit(kzg::commit& commit, const kzg::poly& poly) {
+  kzg::commit again = create_commit(poly);
+  return ECP_equals(&commit.get_curve_point(), &again.get_curve_point());
+}
+
+kzg::proof kzg::trusted_setup::create_proof(const kzg::poly& poly, int byte_offset, int byte_length, int chunk_size) {
+  if (chunk_size > MAX_CHUNK_BYTES) throw invalid_argument("chunk_size must at most MAX_CHUNK_BYTES.");
+  if (byte_offset % chunk_size != 0) throw invalid_argument("byte_offset is not a multiple of chunk_size.");
+  if (byte_length % chunk_size != 0) throw invalid_argument("byte_length is not a multiple of chun_size.");
+  return create_proof(poly, byte_offset / chunk_size, byte_length / chunk_size);
+}
+
+// q = P div prod (x - (chunk_offset + j)) and the MSM over q run back to back on the device
+kzg::proof kzg::trusted_setup::create_proof(const kzg::poly& poly, int chunk_offset, int chunk_length) {
+  if (chunk_length < 1) throw invalid_argument("chunk_length must be 1 or greater");
+  const ZZ_pX& P = poly.get_poly();
+  const long n = deg(P) + 1;
+  if (n <= chunk_length) return kzg::proof(g1_from_body(nullptr, 1));  // zero quotient
+  kzg_gpu_ctx* ctx = device_of(this, _G1, _G2);
+  std::vector<uint8_t> raw = pack_coeffs(P);
+  uint8_t xy[G1_BYTES];
+  int is_inf = 0;
+  int rc = kzg_gpu_prove(ctx, raw.data(), (uint64_t)n, (int64_t)chunk_offset, (uint64_t)chunk_length, xy, &is_inf);
+  if (rc) fail(ctx, rc, "prove");
+  return kzg::proof(g1_from_body(xy, is_inf));
+}
+
+bool kzg::trusted_setup::verify_proof(kzg::commit& commit, kzg::proof& proof, kzg::blob& expected_data) {
+  vector<pair<ZZ_p, ZZ_p>>& points = expected_data.get_data();
+  if (points.size() < 1) throw invalid_argument("expected_data size must be 1 or greater");
+  if (points.size() >= _G1.size()) return false;
+
+  ZZ_pX interp, vanish;
+  linear_roots_and_polyfit(interp, vanish, points);  // host NTL, as in the reference (SURVEY 8(f) N1 moves it)
+
+  ECP2 z_s = polyeval_G2(vanish);                     // device
+  ECP i_s = polyeval_G1(interp);                      // device
+  FP12 lhs, rhs;
+  PAIR_ate(&lhs, &z_s, &proof.get_curve_point());     // e([Z(s)]_2, proof)
+  PAIR_fexp(&lhs);
+  ECP_neg(&i_s);
+  ECP_add(&i_s, &commit.get_curve_point());           // commit - [I(s)]_1
+  PAIR_ate(&rhs, &_G2[0], &i_s);
+  PAIR_fexp(&rhs);
+  return FP12_equals(&lhs, &rhs);
+}
+
+void kzg::trusted_setup::export_setup(const std::string& filename) {
+  std::ofstream file(filename, std::ios::out | std::ios::binary | std::ios::trunc);
+  if (!file.is_open()) {
+    std::cerr << "failed to export" << std::endl;
+    return;
+  }
+  const uint64_t n = _G1.size();
+  std::vector<char> out;
+  out.reserve(8 + n * (size_t)(G1_BYTES + G2_BYTES + 10));
+  auto put = [&](const void* p, size_t len) { out.insert(out.end(), (const char*)p, (const char*)p + len); };
+  put(&n, sizeof n);
+  for (uint64_t i = 0; i < n; i++) {
+    char body[G1_BYTES + 1];
+    octet o = {0, (int)sizeof(body), body};
+    ECP_toOctet(&o, &_G1[i], false);
+    const uint32_t len = (uint32_t)o.len;
+    put(&len, sizeof len);
+    put(o.val, o.len);
+  }
+  for (uint64_t i = 0; i < n; i++) {
+    char body[G2_BYTES + 1];
+    octet o = {0, (int)sizeof(body), body};
+    ECP2_toOctet(&o, &_G2[i], false);
+    const uint32_t len = (uint32_t)o.len;
+    put(&len, sizeof len);
+    put(o.val, o.len);
+  }
+  file.write(out.data(), (std::streamsize)out.size());
+}

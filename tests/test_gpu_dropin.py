@@ -1,0 +1,105 @@
+"""The C++ drop-in (src/trusted_setup_gpu.cpp in place of the reference's src/trusted_setup.cpp, everything
+else of the reference unmodified; built by src/build_dropin.sh into oracle/_ref/dropin/) on a real GPU:
+
+  * the reference's OWN test program (testing/testing.cpp, 36 property checks incl. the two EIP-4844 blobs)
+    and its own benchmark (benchmark/benchmark.cpp) run unchanged on top of the CUDA path;
+  * the byte-file harness (oracle/ref_harness.cpp) linked against the drop-in reproduces the golden vectors
+    the unmodified reference produced (tests/golden), bit for bit, and its verify_proof (device MSMs + host
+    pairings) accepts the golden proofs and rejects tampered data;
+  * cross-verification: proofs made by the drop-in are accepted by the unmodified reference binary.
+"""
+import os
+import re
+import subprocess
+import tempfile
+
+import pytest
+
+from tests.golden_util import CURVE_NAMES, ROOT, load
+
+pytestmark = pytest.mark.gpu
+DROPIN = os.path.join(ROOT, "oracle", "_ref", "dropin")
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+
+def _need(path):
+    if not os.path.exists(path):
+        pytest.skip(f"{os.path.relpath(path, ROOT)} not built (src/build_dropin.sh needs /root/reference)")
+    return path
+
+
+def _run(binary, *args, cwd=None, timeout=600):
+    return subprocess.run([binary, *map(str, args)], check=True, capture_output=True, text=True, cwd=cwd,
+                          timeout=timeout).stdout
+
+
+def test_reference_test_program_on_gpu():
+    """testing/testing.cpp, unmodified, linked against the drop-in: every check must print PASSED."""
+    out = _run(_need(os.path.join(DROPIN, "testing-bn254-gpu")), cwd=DROPIN)
+    plain = re.sub(r"\x1b\[[0-9;]*m", "", out)
+    assert "FAILED" not in plain, plain
+    assert plain.count("PASSED") == 36, plain
+
+
+@pytest.mark.parametrize("cname", ["bn254", "bls12381"])
+def test_reference_benchmark_on_gpu(cname):
+    """benchmark/benchmark.cpp, unmodified: every row verifies (BASELINE config 1 / 5 shapes, on the GPU path)."""
+    out = _run(_need(os.path.join(DROPIN, f"benchmark-{cname}-gpu")), cwd=DROPIN)
+    assert "✗" not in out and "✓" in out, out
+    outdir = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(outdir):  # keep the table next to the other GPU-run artefacts
+        with open(os.path.join(outdir, f"benchmark-{cname}-gpu.txt"), "w") as f:
+            f.write(out)
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_dropin_reproduces_reference_golden_vectors(cname):
+    drop = _need(os.path.join(DROPIN, f"kzgdrop-{cname}"))
+    ref = os.path.join(REF, f"kzgref-{cname}")
+    kat, srs_bytes = load(cname)
+    want = {c["name"]: c for c in kat["cases"]}
+    with tempfile.TemporaryDirectory() as td:
+        f = lambda n: os.path.join(td, n)
+        open(f("srs"), "wb").write(srs_bytes)
+        for name in ("zero", "deg37", "deg46_max", "edge_scalars"):
+            case = want[name]
+            open(f("c"), "wb").write(bytes.fromhex(case["coeffs"]))
+            _run(drop, "commit", f("srs"), f("c"), f("o"))
+            assert open(f("o"), "rb").read().hex() == case["commit"], name
+            _run(drop, "g2msm", f("srs"), f("c"), f("o"))
+            assert open(f("o"), "rb").read().hex() == case["g2msm"], name
+            for op in case["openings"][2:5:2]:
+                off, k = op["off"], op["k"]
+                _run(drop, "prove", f("srs"), f("c"), off, k, f("pf"))
+                assert open(f("pf"), "rb").read().hex() == op["proof"], (name, off, k)
+                open(f("cm"), "wb").write(bytes.fromhex(case["commit"]))
+                open(f("y"), "wb").write(bytes.fromhex(op["ys"]))
+                # the drop-in's verify_proof: device MSMs over Z and I, host pairings
+                assert int(_run(drop, "verify", f("srs"), f("cm"), f("pf"), off, f("y")).strip()) == op["verify"]
+                bad = bytearray(bytes.fromhex(op["ys"]))
+                bad[0] ^= 1
+                open(f("y2"), "wb").write(bytes(bad))
+                assert int(_run(drop, "verify", f("srs"), f("cm"), f("pf"), off, f("y2")).strip()) == op["verify_tampered"]
+                assert int(_run(drop, "verify", f("srs"), f("cm"), f("pf"), off + 1, f("y")).strip()) == op["verify_wrong_offset"]
+                if os.path.exists(ref):  # the unmodified reference accepts the drop-in's proof
+                    assert int(_run(ref, "verify", f("srs"), f("cm"), f("pf"), off, f("y")).strip()) == op["verify"]
+
+
+def test_dropin_trusted_setup_is_loadable_by_reference():
+    """trusted_setup(int) on the device -> export_setup -> the UNMODIFIED reference loads the file, commits to
+    a polynomial with it and gets the same bytes as the drop-in."""
+    cname = "bls12381"
+    drop = _need(os.path.join(DROPIN, f"kzgdrop-{cname}"))
+    ref = _need(os.path.join(REF, f"kzgref-{cname}"))
+    with tempfile.TemporaryDirectory() as td:
+        f = lambda n: os.path.join(td, n)
+        _run(drop, "setup", 40, f("srs"))
+        coeffs = bytes(range(1, 33)) * 30
+        coeffs = b"".join(coeffs[i:i + 31] + b"\x00" for i in range(0, 31 * 30, 31))
+        open(f("c"), "wb").write(coeffs)
+        _run(drop, "commit", f("srs"), f("c"), f("o1"))
+        _run(ref, "commit", f("srs"), f("c"), f("o2"))
+        assert open(f("o1"), "rb").read() == open(f("o2"), "rb").read()
+        _run(drop, "prove", f("srs"), f("c"), 2, 5, f("p1"))
+        _run(ref, "prove", f("srs"), f("c"), 2, 5, f("p2"))
+        assert open(f("p1"), "rb").read() == open(f("p2"), "rb").read()
