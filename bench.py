@@ -55,6 +55,14 @@ def canonical_counts(n, limbs=FP_LIMBS, bits=SCALAR_BITS):
     return {"c": c, "W": W, "modmul_per_point": modmul, "imad_per_point": imad}
 
 
+def workload_config(args):
+    """Same dict on both arms (the driver compares them)."""
+    return {"workload": "BLS12-381 G1 MSM, 2^%d synthetic SRS points per GPU (polyeval_G1); N>1: point-range split + "
+                        "NCCL all-gather of the partial sums + fold" % args.log2n,
+            "curve": CURVE, "points_per_gpu": 1 << args.log2n, "canonical_window_bits": canonical_counts(1 << args.log2n)["c"],
+            "l2": "256 MiB memset flush before every timed step; inputs 128 MiB"}
+
+
 def random_scalars(n, seed):
     import numpy as np
     rng = np.random.default_rng(seed)
@@ -160,7 +168,7 @@ def run_reference(args):
         "impl": "reference", "metric": "g1_msm_points_per_s", "value": value, "unit": "points/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_total / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32 limbs (reference: 58-bit limbs in int64)", "data": "synthetic",
-        "config": {"workload": "BLS12-381 G1 MSM 2^%d (polyeval_G1)" % args.log2n, "curve": CURVE, "points": n},
+        "config": workload_config(args),
         "cpu_baseline": {"value": value, "unit": "points/s", "cores": cores, "kind": "reference",
                          "sample": "%d host processes x create_commit over %d of the 2^%d terms per step (reference MSM is "
                                    "strictly per-term, so points/s is size-independent); harness-level parallelism, the "
@@ -177,6 +185,7 @@ def run_b200(args):
     import numpy as np
     import torch
     import kzg_b200
+    import sharding
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -198,6 +207,7 @@ def run_b200(args):
     ctx = kzg_b200.Context(CURVE, local)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
     ctx.set_option("setup_g2", 0)
+    ctx.set_option("profile", 1)
     ctx.set_option("precompute", args.precompute)
     ctx.set_option("window_bits", args.window_bits)
     # Point-range split: rank g owns n points and its own n scalars of the N*n-term sum.  The synthetic bases of
@@ -210,11 +220,8 @@ def run_b200(args):
 
     def fold_partials():
         """N > 1: all-gather the projective partial sums (NCCL) and fold them on every rank."""
-        part = ctx.msm_fetch_partial()
-        t = torch.frombuffer(bytearray(part), dtype=torch.uint8).cuda()
-        allp = [torch.empty_like(t) for _ in range(world)]
-        dist.all_gather(allp, t)
-        return ctx.g1_sum_partials([bytes(p.cpu().numpy()) for p in allp])
+        parts = sharding.gather_partials(dist, ctx.msm_fetch_partial(), device=torch.device("cuda", local))
+        return ctx.g1_sum_partials(parts)
 
     def step_resident():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -325,9 +332,7 @@ def run_b200(args):
             "metric": "g1_msm_points_per_s", "value": value, "unit": "points/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32 limbs (Montgomery, 12x32-bit Fp / 8x32-bit Fr)", "data": "synthetic",
-            "config": {"workload": "BLS12-381 G1 MSM 2^%d per GPU (polyeval_G1), point-range split + partial-sum fold for N>1"
-                                   % args.log2n, "curve": CURVE, "points_per_gpu": n, "window_bits": cc["c"] if not args.window_bits else args.window_bits,
-                       "precompute": args.precompute, "l2": "256 MiB memset flush before every timed step; inputs 128 MiB"},
+            "config": workload_config(args),
             "e2e": {"value": e2e_value, "unit": "points/s", "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": 96 + 4,
                     "ms_per_step": total_e2e_ms / args.steps},
             "gpu_launches": gpu_launches,

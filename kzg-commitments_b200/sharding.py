@@ -1,0 +1,31 @@
+"""Rank-side logic of the two multi-GPU shardings; one process per GPU.
+
+1. independent blobs, no collective:   blob_slice(rank, world, batch)
+2. point-range split of one large MSM: point_range(rank, world, n) + gather_partials(...) — every rank ends
+   with all `world` projective partial sums (4*L words each) in rank order and folds them locally
+   (kzg_gpu_g1_sum_partials); EC addition is not an NCCL reduction op, hence all-gather + local fold.
+"""
+
+
+def blob_slice(rank, world, batch):
+    """Contiguous share of `batch` independent blobs owned by `rank` (sizes differ by at most one)."""
+    base, extra = divmod(batch, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def point_range(rank, world, n):
+    """Contiguous range of points/scalars of an n-term MSM owned by `rank`."""
+    return blob_slice(rank, world, n)
+
+
+def gather_partials(dist, partial_bytes, device=None):
+    """All-gather one fixed-size byte string per rank (NCCL on `device`, or gloo on the CPU when device is None).
+    Returns the list of byte strings in rank order."""
+    import torch
+    t = torch.frombuffer(bytearray(partial_bytes), dtype=torch.uint8)
+    if device is not None:
+        t = t.to(device)
+    out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return [bytes(o.cpu().numpy().tobytes()) for o in out]
