@@ -122,7 +122,7 @@ struct Ctx final : kzg_gpu_ctx {
   bool fb_ready = false;
   // scratch
   DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
-      out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, red0, red1, red2, red3;
+      out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3;
   // description of the most recent launch, for fetch()
   uint64_t last_batch = 0;
   int last_group = 1;
@@ -131,7 +131,7 @@ struct Ctx final : kzg_gpu_ctx {
     cudaSetDevice(device);
     for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
-                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &red0, &red1, &red2, &red3})
+                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &red0, &red1, &red2, &red3})
       b->release();
     for (cudaEvent_t e : phase_ev) if (e) cudaEventDestroy(e);
     if (stream) cudaStreamDestroy(stream);
@@ -272,11 +272,11 @@ struct Ctx final : kzg_gpu_ctx {
     const uint64_t red_cap = groups * ((uint64_t)sh.nb / 2 + R + Cn + 2);
 
     CK(digits.ensure(records * 4));
+    CK(ranks.ensure(records * 4));
     CK(sorted.ensure(records * 4));
     CK(counts.ensure((nbuckets + 1) * 4));
     CK(starts.ensure((nbuckets + 1) * 4));
     CK(task_first.ensure((nbuckets + 1) * 4));
-    CK(cursor.ensure((nbuckets + 1) * 4));
     CK(hist.ensure((3 * (MSM_MAX_CHUNK + 1) + 1) * 4));
     CK(slot_seg.ensure(max_tasks * sizeof(MsmSlotSeg)));
     CK(tasks.ensure(max_tasks * sizeof(MsmTask)));
@@ -297,14 +297,14 @@ struct Ctx final : kzg_gpu_ctx {
     {
       const uint64_t total = count * batch;
       unsigned grid = (unsigned)std::min<uint64_t>((total + 255) / 256, (uint64_t)sms * 16);
-      msm_digits<C><<<grid, 256, 0, stream>>>(sh, d_scalars, digits.as<int32_t>(), counts.as<uint32_t>());
+      msm_digits<C><<<grid, 256, 0, stream>>>(sh, d_scalars, digits.as<int32_t>(), ranks.as<uint32_t>(), counts.as<uint32_t>());
       LAUNCHED();
     }
-    int rc = enqueue_scan(nbuckets, 0, counts.as<uint32_t>(), starts.as<uint32_t>(), cursor.as<uint32_t>());
+    int rc = enqueue_scan(nbuckets, 0, counts.as<uint32_t>(), starts.as<uint32_t>(), nullptr);
     if (rc) return rc;
     {
       unsigned grid = (unsigned)std::min<uint64_t>((records + 255) / 256, (uint64_t)sms * 32);
-      msm_scatter<<<grid, 256, 0, stream>>>(sh, digits.as<int32_t>(), starts.as<uint32_t>(), cursor.as<uint32_t>(),
+      msm_scatter<<<grid, 256, 0, stream>>>(sh, digits.as<int32_t>(), starts.as<uint32_t>(), ranks.as<uint32_t>(),
                                             sorted.as<uint32_t>());
       LAUNCHED();
     }

@@ -106,6 +106,7 @@ KZG_HDN int check_field(Lcg& g) {
   bad += !(F::add(a, F::neg(a)).is_zero());
   bad += !(F::to_mont(F::from_mont(a)) == a);
   if (!a.is_zero()) bad += !(F::mul(a, F::inv(a)) == F::one());
+  bad += !(F::inv(a) == F::inv_fermat(a));  // binary-GCD inverse against the Fermat ladder
   return bad;
 }
 

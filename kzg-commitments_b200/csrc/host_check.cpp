@@ -69,16 +69,17 @@ int msm_host(uint64_t srs_n, const uint8_t* pts_bytes, const uint8_t* scalars, u
   const uint64_t records = count * batch * sh.W;
   const uint64_t nbuckets = sh.total_buckets();
   std::vector<int32_t> digits(records);
+  std::vector<uint32_t> ranks(records);
   std::vector<uint32_t> counts(nbuckets + 1, 0), starts(nbuckets + 1), task_first(nbuckets + 1), cursor(nbuckets + 1, 0),
       sorted(records);
-  for (uint64_t t = 0; t < count * batch; t++) msm_digits_thread<C>(sh, scalars, digits.data(), counts.data(), t);
+  for (uint64_t t = 0; t < count * batch; t++) msm_digits_thread<C>(sh, scalars, digits.data(), ranks.data(), counts.data(), t);
   uint32_t a = 0, b = 0;
   for (uint64_t i = 0; i < nbuckets; i++) {
     starts[i] = a; task_first[i] = b;
     a += counts[i]; b += (counts[i] + chunk - 1) / chunk;
   }
   starts[nbuckets] = a; task_first[nbuckets] = b;
-  for (uint64_t t = 0; t < records; t++) msm_scatter_thread(sh, digits.data(), starts.data(), cursor.data(), sorted.data(), t);
+  for (uint64_t t = 0; t < records; t++) msm_scatter_thread(sh, digits.data(), starts.data(), ranks.data(), sorted.data(), t);
   // tasks ordered by descending length (msm_task_hist / msm_task_place)
   std::vector<uint32_t> hist(MSM_MAX_CHUNK + 2, 0), hist_start(MSM_MAX_CHUNK + 1), hcur(MSM_MAX_CHUNK + 1, 0);
   for (uint64_t i = 0; i < nbuckets; i++) msm_task_hist_thread(chunk, starts.data(), task_first.data(), hist.data(), i);

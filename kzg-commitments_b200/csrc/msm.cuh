@@ -97,7 +97,8 @@ KZG_HD uint32_t scalar_bits(const uint32_t* k, int pos, int width) {
 // ---------------------------------------------------------------- 1. digits + histogram
 // digits[(blob*W + w) * n + i] = signed digit ; counts[key]++ for non-zero digits
 template <class C>
-KZG_HD void msm_digits_thread(const MsmShape& sh, const uint8_t* scalars, int32_t* digits, uint32_t* counts, uint64_t t) {
+KZG_HD void msm_digits_thread(const MsmShape& sh, const uint8_t* scalars, int32_t* digits, uint32_t* ranks, uint32_t* counts,
+                              uint64_t t) {
   const uint64_t blob = t / sh.n, i = t - blob * sh.n;
   uint32_t k[C::FrP::L];
   load_scalar<C>(scalars, t, k);
@@ -112,18 +113,20 @@ KZG_HD void msm_digits_thread(const MsmShape& sh, const uint8_t* scalars, int32_
     if (d != 0) {
       const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
       const uint64_t group = blob * sh.groups_per_msm + (sh.precomp ? 0 : w);
-      atomic_inc_u32(&counts[group * sh.nb + (mag - 1)]);
+      // the value returned by the histogram increment is this record's rank inside its bucket: the
+      // scatter pass then needs no second round of atomics
+      ranks[(blob * sh.W + w) * sh.n + i] = atomic_inc_u32(&counts[group * sh.nb + (mag - 1)]);
     }
   }
 }
 #if defined(__CUDACC__)
 template <class C>
 __global__ void msm_digits(MsmShape sh, const uint8_t* __restrict__ scalars, int32_t* __restrict__ digits,
-                           uint32_t* __restrict__ counts) {
+                           uint32_t* __restrict__ ranks, uint32_t* __restrict__ counts) {
   const uint64_t total = sh.n * sh.batch;
   for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total;
        t += (uint64_t)gridDim.x * blockDim.x)
-    msm_digits_thread<C>(sh, scalars, digits, counts, t);
+    msm_digits_thread<C>(sh, scalars, digits, ranks, counts, t);
 }
 #endif
 
@@ -214,7 +217,7 @@ scan_apply(uint64_t n, int chunk, const uint32_t* __restrict__ in, const uint32_
 
 // ---------------------------------------------------------------- 3. scatter (counting sort)
 // record = source index | sign << 31
-KZG_HD void msm_scatter_thread(const MsmShape& sh, const int32_t* digits, const uint32_t* starts, uint32_t* cursor,
+KZG_HD void msm_scatter_thread(const MsmShape& sh, const int32_t* digits, const uint32_t* starts, const uint32_t* ranks,
                                uint32_t* sorted, uint64_t t) {
   const int32_t d = digits[t];
   if (d == 0) return;
@@ -224,17 +227,17 @@ KZG_HD void msm_scatter_thread(const MsmShape& sh, const int32_t* digits, const 
   const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
   const uint64_t group = blob * sh.groups_per_msm + (sh.precomp ? 0 : w);
   const uint64_t key = group * sh.nb + (mag - 1);
-  const uint32_t pos = starts[key] + atomic_inc_u32(&cursor[key]);
+  const uint32_t pos = starts[key] + ranks[t];
   const uint64_t src = sh.precomp ? ((uint64_t)w * sh.table_stride + sh.base_offset + i) : (sh.base_offset + i);
   sorted[pos] = (uint32_t)src | (d < 0 ? 0x80000000u : 0u);
 }
 #if defined(__CUDACC__)
 static __global__ void msm_scatter(MsmShape sh, const int32_t* __restrict__ digits, const uint32_t* __restrict__ starts,
-                            uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
+                            const uint32_t* __restrict__ ranks, uint32_t* __restrict__ sorted) {
   const uint64_t total = sh.n * sh.batch * (uint64_t)sh.W;
   for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total;
        t += (uint64_t)gridDim.x * blockDim.x)
-    msm_scatter_thread(sh, digits, starts, cursor, sorted, t);
+    msm_scatter_thread(sh, digits, starts, ranks, sorted, t);
 }
 #endif
 
@@ -400,7 +403,7 @@ msm_fold_level(int level, const uint32_t* __restrict__ ntasks_ptr, const uint32_
 // per level, rows and columns side by side in blockIdx.y), and the two short weighted sums run in
 // chunks of WCHUNK terms (running sums + a double-and-add correction for the chunk offset) followed
 // by the same pairwise trees.  All lengths are powers of two.
-constexpr int WCHUNK = 4;  // terms per thread of the weighted sums
+constexpr int WCHUNK = 2;  // terms per thread of the weighted sums
 
 // level 0 of a row/column tree, reading bucket values through task_first:
 // out[(g*nsums + s)*P + p] = B[g*nb + s*sstride + 2p*jstride] + B[.. + (2p+1)*jstride],  P = max(len/2, 1)
