@@ -117,6 +117,10 @@ uint64_t kzg_gpu_launch_count(const kzg_gpu_ctx* ctx);
  * digits+sort+tasks, bucket accumulation, bucket reduction, finish (affine + bytes).  n >= 4. */
 int kzg_gpu_phase_times(kzg_gpu_ctx* ctx, float* ms, int n);
 
+/* Shape of the most recent MSM pass, out[0..5] = records (non-trivial window digits incl. zeros), buckets, tasks,
+ * most tasks in one bucket, window bits c, task chunk.  n >= 6. */
+int kzg_gpu_msm_stats(kzg_gpu_ctx* ctx, uint64_t* out, int n);
+
 /* Integer-pipe microbenchmarks used for the roofline denominator:
  * kind 0: independent mad.lo.cc/madc.hi.cc chains (-> IMAD.WIDE.U32.X), returns 32x32 products/s
  * kind 1: independent plain 32-bit IMAD (mad.lo.u32), returns instructions/s

@@ -112,6 +112,7 @@ void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx) { return ctx ? (void*)ctx->stream : n
 uint64_t kzg_gpu_launch_count(const kzg_gpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
 int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops) { return ctx ? ctx->microbench(kind, ops) : KZG_GPU_ERR_ARG; }
 int kzg_gpu_phase_times(kzg_gpu_ctx* ctx, float* ms, int n) { return ctx ? ctx->phase_times(ms, n) : KZG_GPU_ERR_ARG; }
+int kzg_gpu_msm_stats(kzg_gpu_ctx* ctx, uint64_t* out, int n) { return ctx ? ctx->msm_stats(out, n) : KZG_GPU_ERR_ARG; }
 int kzg_gpu_selftest(kzg_gpu_ctx* ctx, int* failures) { return ctx ? ctx->selftest(failures) : KZG_GPU_ERR_ARG; }
 
 }  // extern "C"

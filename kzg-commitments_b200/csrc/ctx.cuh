@@ -81,6 +81,7 @@ struct kzg_gpu_ctx {
   virtual int microbench(int kind, double* ops) = 0;
   virtual int selftest(int* failures) = 0;
   virtual int phase_times(float* ms, int n) = 0;
+  virtual int msm_stats(uint64_t* out, int n) = 0;
 
   int cuda_fail(cudaError_t e, const char* where) {
     char buf[256];
@@ -145,7 +146,7 @@ struct Ctx final : kzg_gpu_ctx {
   }
 
   // ------------------------------------------------------------------ SRS
-  // window width of the per-SRS table: minimise  n*W*10 + 2^(c-1)*40  modmuls (mixed adds + bucket
+  // window width of the per-SRS table: minimise  n*W*10 + 2^(c-1)*30  modmuls (mixed adds + bucket
   // reduction) for an MSM over the whole SRS, subject to W <= MAXW and a table-size budget.
   int pick_table_c(uint64_t n) const {
     if (opt_window_bits) return opt_window_bits;
@@ -155,7 +156,7 @@ struct Ctx final : kzg_gpu_ctx {
       const int W = (C::SCALAR_BITS + 1 + c - 1) / c;
       if (W > MAXW) continue;
       if ((double)W * n * sizeof(Affine<Fp>) > 24e9) continue;
-      const double cost = (double)n * W * 10.0 + (double)(1ull << (c - 1)) * 40.0;
+      const double cost = (double)n * W * 10.0 + (double)(1ull << (c - 1)) * 30.0;
       if (!best || cost < best_cost) { best = c; best_cost = cost; }
     }
     return best ? best : 8;
@@ -262,7 +263,7 @@ struct Ctx final : kzg_gpu_ctx {
     const uint64_t records = count * batch * (uint64_t)sh.W;
     // task length: long enough to amortise the fold, short enough that a small MSM still fills the machine
     sh.chunk = opt_task_chunk ? std::min(opt_task_chunk, MSM_MAX_CHUNK)
-                              : (int)std::min<uint64_t>(48, std::max<uint64_t>(4, records / 65536));
+                              : (int)std::min<uint64_t>(128, std::max<uint64_t>(4, records / 65536));
     if (records >= (1ull << 31) || (precomp && (uint64_t)sh.W * srs_n >= (1ull << 31))) return KZG_GPU_ERR_ARG;
     const uint64_t nbuckets = sh.total_buckets();
     const uint64_t max_tasks = records / sh.chunk + nbuckets + 1;
@@ -373,6 +374,7 @@ struct Ctx final : kzg_gpu_ctx {
     LAUNCHED();
     phase_mark(4);
     last_batch = batch;
+    last_records = records; last_nbuckets = nbuckets; last_c = sh.c; last_chunk = sh.chunk;
     return KZG_GPU_OK;
   }
 
@@ -617,6 +619,21 @@ struct Ctx final : kzg_gpu_ctx {
     if (!opt_profile) return KZG_GPU_ERR_STATE;
     CK(cudaEventSynchronize(phase_ev[4]));
     for (int i = 0; i < 4; i++) CK(cudaEventElapsedTime(&ms[i], phase_ev[i], phase_ev[i + 1]));
+    return KZG_GPU_OK;
+  }
+  // shape of the most recent MSM pass: records, buckets, tasks, most tasks in one bucket, window bits, task chunk
+  uint64_t last_records = 0, last_nbuckets = 0;
+  int last_c = 0, last_chunk = 0;
+  int msm_stats(uint64_t* out, int n) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!out || n < 6) return KZG_GPU_ERR_ARG;
+    if (!last_nbuckets) return KZG_GPU_ERR_STATE;
+    uint32_t ntasks = 0, max_nt = 0;
+    CK(cudaMemcpyAsync(&ntasks, task_first.as<uint32_t>() + last_nbuckets, 4, cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(&max_nt, hist.as<uint32_t>() + MSM_MAX_CHUNK + 1, 4, cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    out[0] = last_records; out[1] = last_nbuckets; out[2] = ntasks; out[3] = max_nt; out[4] = (uint64_t)last_c; out[5] = (uint64_t)last_chunk;
     return KZG_GPU_OK;
   }
   int microbench(int kind, double* ops) override {

@@ -71,6 +71,7 @@ def load_library():
         "kzg_gpu_microbench": (ctypes.c_int, [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
         "kzg_gpu_selftest": (ctypes.c_int, [vp, ip]),
         "kzg_gpu_phase_times": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_float), ctypes.c_int]),
+        "kzg_gpu_msm_stats": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)  # AttributeError if the library does not export the declared symbol
@@ -86,7 +87,7 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_msm_g2", "kzg_gpu_msm_g1_batch", "kzg_gpu_msm_g1_launch", "kzg_gpu_msm_fetch",
     "kzg_gpu_msm_fetch_partial", "kzg_gpu_g1_sum_partials", "kzg_gpu_poly_quotient", "kzg_gpu_poly_eval_range",
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
-    "kzg_gpu_phase_times",
+    "kzg_gpu_phase_times", "kzg_gpu_msm_stats",
 ]
 
 
@@ -242,6 +243,12 @@ class Context:
         if rc != 0:
             return None
         return dict(zip(("sort", "accumulate", "reduce", "finish"), [float(v) for v in ms]))
+
+    def msm_stats(self):
+        out = (ctypes.c_uint64 * 6)()
+        if self.lib.kzg_gpu_msm_stats(self.h, out, 6) != 0:
+            return None
+        return dict(zip(("records", "buckets", "tasks", "max_tasks_per_bucket", "window_bits", "task_chunk"), [int(v) for v in out]))
 
     def selftest(self):
         f = ctypes.c_int(-1)

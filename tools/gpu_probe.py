@@ -64,7 +64,7 @@ def main():
                     xy, inf = ctx.msm_fetch(1)
                     row = {"log2n": lg, "precompute": pre, "window_bits": wb, "task_chunk": ch, "ms": min(times[1:]),
                            "first_ms": times[0], "mpts_per_s": n / min(times[1:]) / 1e3, "setup_s": t_setup,
-                           "xy": xy[:8].hex(), "phases": ctx.phase_times()}
+                           "xy": xy[:8].hex(), "phases": ctx.phase_times(), "stats": ctx.msm_stats()}
                     res["msm"].append(row)
                     print(json.dumps(row), flush=True)
     if args.out:
