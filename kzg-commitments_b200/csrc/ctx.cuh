@@ -487,10 +487,27 @@ struct Ctx final : kzg_gpu_ctx {
   }
   // quotient of poly0 by the k consecutive roots -> qbytes (device, (n-k)*SB bytes)
   int enqueue_quotient(uint64_t n, int64_t first_root, uint64_t k) {
-    constexpr int QT = 512;
-    poly_quotient_rounds<C, QT><<<1, QT, 0, stream>>>(n, (long long)first_root, k, poly0.as<Fr>(), poly1.as<Fr>());
-    LAUNCHED();
-    const Fr* q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
+    const Fr* q;
+    if (k < 48) {  // a few opened points: one CTA-wide suffix scan per root
+      constexpr int QT = 512;
+      poly_quotient_rounds<C, QT><<<1, QT, 0, stream>>>(n, (long long)first_root, k, poly0.as<Fr>(), poly1.as<Fr>());
+      LAUNCHED();
+      q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
+    } else {       // many: systolic passes of up to ST roots, ping-ponging between the two buffers
+      constexpr int ST = 512, CHK = 256;
+      Fr* src = poly0.as<Fr>();
+      Fr* dst = poly1.as<Fr>();
+      uint64_t m = n, done = 0;
+      while (done < k) {
+        const int t = (int)std::min<uint64_t>(ST, k - done);
+        poly_quotient_systolic<C, ST, CHK><<<1, ST, 0, stream>>>(m, (long long)first_root + (long long)done, t, src, dst);
+        LAUNCHED();
+        std::swap(src, dst);
+        m -= t;
+        done += t;
+      }
+      q = src;
+    }
     const uint64_t nq = n - k;
     CK(qbytes.ensure(nq * (size_t)SB));
     unsigned grid = (unsigned)std::min<uint64_t>((nq + 127) / 128, 148 * 8);

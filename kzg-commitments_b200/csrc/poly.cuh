@@ -125,6 +125,46 @@ poly_quotient_rounds(uint64_t n, long long first_root, uint64_t k, Field<typenam
   }
 }
 
+// ---------------------------------------------------------------- quotient, many roots: systolic pipeline
+// The scan kernel above costs one CTA-wide scan per root (~70 us), fine for a handful of opened points
+// but not for the multi-proof rows (k = 128 ... 4096).  Here thread j is the synthetic-division stage
+// of root first_root + j:  y = x + a_j * carry;  carry = y.  The coefficient stream enters stage 0
+// top-down, stage j consumes what stage j-1 produced one step earlier and drops its own last output
+// (the remainder), so `t` roots are divided out in m + t steps of ONE modmul each instead of t scans.
+// One CTA, T stages per pass; the host chains passes for k > T.  dst receives m - t coefficients.
+template <class C, int T, int CHK>
+__global__ void __launch_bounds__(T)
+poly_quotient_systolic(uint64_t m, long long first_root, int t, const Field<typename C::FrP>* __restrict__ src,
+                       Field<typename C::FrP>* __restrict__ dst) {
+  using Fr = Field<typename C::FrP>;
+  __shared__ Fr link[2][T];
+  __shared__ Fr feed[CHK];
+  const int j = threadIdx.x;
+  const Fr a = fr_from_i64<C>(first_root + (long long)j);
+  Fr carry = Fr::zero();
+  const uint64_t steps = m + (uint64_t)t;
+  for (uint64_t s = 0; s < steps; s++) {
+    if (s % CHK == 0) {  // refill the feed of stage 0: src top-down, CHK coefficients at a time
+      for (int q = j; q < CHK; q += T) {
+        const uint64_t idx = s + (uint64_t)q;
+        if (idx < m) feed[q] = src[m - 1 - idx];
+      }
+      __syncthreads();
+    }
+    const long long u = (long long)s - j;  // index of this stage's input within its stream
+    if (j < t && u >= 0 && (uint64_t)u < m - (uint64_t)j) {
+      const Fr x = (j == 0) ? feed[s % CHK] : link[s & 1][j - 1];
+      const Fr y = Fr::add(x, Fr::mul(a, carry));
+      carry = y;
+      if ((uint64_t)u + 1 < m - (uint64_t)j) {  // the last output of a stage is the remainder: dropped
+        if (j == t - 1) dst[(m - (uint64_t)t - 1) - (uint64_t)u] = y;
+        else link[(s + 1) & 1][j] = y;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // ---------------------------------------------------------------- evaluation at consecutive points
 // One CTA per point: thread t Horner-evaluates its slice, scales by x^lo, CTA tree-sums.
 template <class C, int THREADS>

@@ -280,3 +280,24 @@ def test_msm_2_16_linearity_and_oracle(ctxs):
     xa2, _ = ctx.msm_g1(C.scalars_to_bytes(a), n)
     ctx.set_option("precompute", 0)
     assert xa2 == xa
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_quotient_many_roots_systolic(ctxs, cname):
+    """A6 with many opened points (multi-proof rows of benchmark.cpp): the systolic kernel, one pass (k = 64, 512),
+    chained passes (k = 700, 1300) and the boundary with the scan kernel (k = 47, 48), against the oracle."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(77 + C.id)
+    n = 1501
+    coeffs = [rng.randrange(C.r) for _ in range(n)]
+    raw = C.scalars_to_bytes(coeffs)
+    for off, k in ((0, 47), (0, 48), (3, 64), (10, 512), (1, 700), (5, 1300), (0, 1500)):
+        q, _, _ = C.poly_quotient(coeffs, off, k)
+        assert ctx.poly_quotient(raw, off, k) == C.scalars_to_bytes(q), (off, k)
+    # proof through the chained path equals [q(s)]G
+    s = rng.randrange(C.r)
+    ts = kzg_b200.TrustedSetup.generate(cname, n + 1, s, ctx=ctx)
+    P = kzg_b200.Poly(ctx, coeffs)
+    q, _, _ = C.poly_quotient(coeffs, 2, 600)
+    assert ts.create_proof(P, 2, 600).serialize() == C.serialize_g1(C.mul(C.poly_eval(q, s), C.g1))
