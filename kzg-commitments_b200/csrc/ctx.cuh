@@ -13,11 +13,13 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "curve_constants.cuh"
 #include "diag.cuh"
 #include "msm.cuh"
+#include "msm_affine.cuh"
 #include "poly.cuh"
 #include "setup.cuh"
 
@@ -63,8 +65,8 @@ struct kzg_gpu_ctx {
   uint64_t launches = 0;
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
-  int opt_window_bits = 0, opt_precompute = 1, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0;
+  int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
+      opt_profile = 0, opt_affine_levels = -1;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -123,7 +125,8 @@ struct Ctx final : kzg_gpu_ctx {
   bool fb_ready = false;
   // scratch
   DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
-      out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3;
+      out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3, aff_off, aff_a, aff_b, aff_prefix,
+      aff_totals;
   // description of the most recent launch, for fetch()
   uint64_t last_batch = 0;
   int last_group = 1;
@@ -132,7 +135,7 @@ struct Ctx final : kzg_gpu_ctx {
     cudaSetDevice(device);
     for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
-                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &red0, &red1, &red2, &red3})
+                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &red0, &red1, &red2, &red3})
       b->release();
     for (cudaEvent_t e : phase_ev) if (e) cudaEventDestroy(e);
     if (stream) cudaStreamDestroy(stream);
@@ -262,11 +265,17 @@ struct Ctx final : kzg_gpu_ctx {
     sh.base_offset = base_offset;
     const uint64_t records = count * batch * (uint64_t)sh.W;
     // task length: long enough to amortise the fold, short enough that a small MSM still fills the machine
+    // Batched-affine pre-reduction levels ("affine_levels" option).  OFF by default: measured on B200 at 2^20
+    // (profiles/r1f_affine_levels.md) two levels cost 6.1 ms against the 3.7 ms of XYZZ additions they replace —
+    // each level gathers its inputs twice (forward and backward pass) from the 1.25 GiB window table and is bound
+    // by random-gather bandwidth, while the XYZZ kernel hides one gather behind 10 modmuls.
+    int levels = 0;
+    if (std::is_same<F, Fp>::value) levels = opt_affine_levels >= 0 ? opt_affine_levels : 0;
     sh.chunk = opt_task_chunk ? std::min(opt_task_chunk, MSM_MAX_CHUNK)
-                              : (int)std::min<uint64_t>(128, std::max<uint64_t>(4, records / 65536));
+                              : (int)std::min<uint64_t>(128, std::max<uint64_t>(4, (records >> levels) / 65536));
     if (records >= (1ull << 31) || (precomp && (uint64_t)sh.W * srs_n >= (1ull << 31))) return KZG_GPU_ERR_ARG;
     const uint64_t nbuckets = sh.total_buckets();
-    const uint64_t max_tasks = records / sh.chunk + nbuckets + 1;
+    const uint64_t max_tasks = ((records >> levels) + nbuckets) / sh.chunk + nbuckets + 1;
     const uint64_t groups = sh.total_groups();
     const int h = (sh.c - 1) / 2;
     const uint64_t Cn = 1ull << h, R = (uint64_t)sh.nb / Cn;
@@ -278,6 +287,13 @@ struct Ctx final : kzg_gpu_ctx {
     CK(counts.ensure((nbuckets + 1) * 4));
     CK(starts.ensure((nbuckets + 1) * 4));
     CK(task_first.ensure((nbuckets + 1) * 4));
+    if (levels > 0) {
+      CK(aff_off.ensure((size_t)levels * (nbuckets + 1) * 4));
+      CK(aff_a.ensure(((records >> 1) + nbuckets) * sizeof(Affine<F>)));
+      if (levels > 1) CK(aff_b.ensure(((records >> 2) + nbuckets) * sizeof(Affine<F>)));
+      CK(aff_prefix.ensure(((records >> 1) + nbuckets) * sizeof(F)));
+      CK(aff_totals.ensure((((records >> 1) + nbuckets) / AFF_K + 2) * sizeof(F)));
+    }
     CK(hist.ensure((3 * (MSM_MAX_CHUNK + 1) + 1) * 4));
     CK(slot_seg.ensure(max_tasks * sizeof(MsmSlotSeg)));
     CK(tasks.ensure(max_tasks * sizeof(MsmTask)));
@@ -309,15 +325,41 @@ struct Ctx final : kzg_gpu_ctx {
                                             sorted.as<uint32_t>());
       LAUNCHED();
     }
-    rc = enqueue_scan(nbuckets, sh.chunk, counts.as<uint32_t>(), task_first.as<uint32_t>(), nullptr);
+    // batched-affine pre-reduction (G1 only): `levels` rounds of pairwise affine additions inside the buckets
+    const uint32_t* seg_off = starts.as<uint32_t>();
+    const uint32_t* seg_sorted = sorted.as<uint32_t>();
+    const Affine<F>* seg_pts = precomp ? table : bases;
+    if constexpr (std::is_same<F, Fp>::value) {
+      for (int l = 1; l <= levels; l++) {
+        uint32_t* off_l = aff_off.as<uint32_t>() + (size_t)(l - 1) * (nbuckets + 1);
+        rc = enqueue_scan(nbuckets, 1 << l, counts.as<uint32_t>(), off_l, nullptr);
+        if (rc) return rc;
+        const uint64_t cap = (records >> l) + nbuckets;  // bound on sum ceil(cnt / 2^l)
+        const uint64_t nthreads = (cap + AFF_K - 1) / AFF_K;
+        AffLevel<F> lv{seg_sorted, seg_pts, seg_off, off_l, nbuckets, (l & 1) ? aff_a.as<Affine<F>>() : aff_b.as<Affine<F>>(),
+                       aff_prefix.as<F>(), aff_totals.as<F>()};
+        aff_forward<F><<<(unsigned)((nthreads + 127) / 128), 128, 0, stream>>>(lv, nthreads);
+        LAUNCHED();
+        constexpr int K2 = 4;
+        const uint64_t inv_threads = (nthreads + K2 - 1) / K2;
+        aff_invert<F, K2><<<(unsigned)((inv_threads + 127) / 128), 128, 0, stream>>>(off_l + nbuckets, aff_totals.as<F>());
+        LAUNCHED();
+        aff_backward<F><<<(unsigned)((nthreads + 127) / 128), 128, 0, stream>>>(lv, nthreads);
+        LAUNCHED();
+        seg_sorted = nullptr;
+        seg_pts = lv.out_pts;
+        seg_off = off_l;
+      }
+    }
+    rc = enqueue_scan(nbuckets, sh.chunk << levels, counts.as<uint32_t>(), task_first.as<uint32_t>(), nullptr);
     if (rc) return rc;
     {
       unsigned grid = (unsigned)std::min<uint64_t>((nbuckets + 255) / 256, (uint64_t)sms * 8);
-      msm_task_hist<<<grid, 256, 0, stream>>>(nbuckets, sh.chunk, starts.as<uint32_t>(), task_first.as<uint32_t>(), d_hist);
+      msm_task_hist<<<grid, 256, 0, stream>>>(nbuckets, sh.chunk, seg_off, task_first.as<uint32_t>(), d_hist);
       LAUNCHED();
       msm_task_hist_scan<<<1, 32, 0, stream>>>(d_hist, d_hist_start, d_hist_cursor);
       LAUNCHED();
-      msm_task_place<<<grid, 256, 0, stream>>>(nbuckets, sh.chunk, starts.as<uint32_t>(), task_first.as<uint32_t>(),
+      msm_task_place<<<grid, 256, 0, stream>>>(nbuckets, sh.chunk, seg_off, task_first.as<uint32_t>(),
                                                d_hist_start, d_hist_cursor, tasks.as<MsmTask>(),
                                                slot_seg.as<MsmSlotSeg>());
       LAUNCHED();
@@ -325,16 +367,16 @@ struct Ctx final : kzg_gpu_ctx {
     phase_mark(1);
     {
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)1 << 30);
-      msm_accumulate<F><<<grid, 128, 0, stream>>>(task_first.as<uint32_t>() + nbuckets, tasks.as<MsmTask>(),
-                                                  sorted.as<uint32_t>(), precomp ? table : bases, partial.as<XYZZ<F>>());
+      msm_accumulate<F><<<grid, 128, 0, stream>>>(task_first.as<uint32_t>() + nbuckets, tasks.as<MsmTask>(), seg_sorted,
+                                                  seg_pts, partial.as<XYZZ<F>>());
       LAUNCHED();
     }
     phase_mark(2);
     {
-      int levels = 0;
-      while ((1ull << levels) < max_tasks && levels < 31) levels++;  // bound on ceil(log2(max tasks in a bucket))
+      int fold_levels = 0;
+      while ((1ull << fold_levels) < max_tasks && fold_levels < 31) fold_levels++;  // bound on ceil(log2(max tasks in a bucket))
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 32);
-      for (int l = 0; l < levels; l++) {
+      for (int l = 0; l < fold_levels; l++) {
         msm_fold_level<F><<<grid, 128, 0, stream>>>(l, task_first.as<uint32_t>() + nbuckets, d_hist + MSM_MAX_CHUNK + 1,
                                                     slot_seg.as<MsmSlotSeg>(), partial.as<XYZZ<F>>());
         LAUNCHED();

@@ -11,6 +11,7 @@
 #include "curve_constants.cuh"
 #include "diag.cuh"
 #include "msm.cuh"
+#include "msm_affine.cuh"
 
 using namespace kzgb200;
 
@@ -73,30 +74,53 @@ int msm_host(uint64_t srs_n, const uint8_t* pts_bytes, const uint8_t* scalars, u
   std::vector<uint32_t> counts(nbuckets + 1, 0), starts(nbuckets + 1), task_first(nbuckets + 1), cursor(nbuckets + 1, 0),
       sorted(records);
   for (uint64_t t = 0; t < count * batch; t++) msm_digits_thread<C>(sh, scalars, digits.data(), ranks.data(), counts.data(), t);
+  const int levels = (CoordCount<F>::value == 2) ? (bpc & 3) : 0;  // affine pre-reduction levels (G1 only)
   uint32_t a = 0, b = 0;
   for (uint64_t i = 0; i < nbuckets; i++) {
     starts[i] = a; task_first[i] = b;
-    a += counts[i]; b += (counts[i] + chunk - 1) / chunk;
+    a += counts[i]; b += scan_value(counts[i], chunk << levels);
   }
   starts[nbuckets] = a; task_first[nbuckets] = b;
   for (uint64_t t = 0; t < records; t++) msm_scatter_thread(sh, digits.data(), starts.data(), ranks.data(), sorted.data(), t);
+  // batched-affine pre-reduction (msm_affine.cuh), loops in place of launches
+  const uint32_t* seg_off = starts.data();
+  const uint32_t* seg_sorted = sorted.data();
+  const Affine<F>* seg_pts = precomp ? table.data() : bases.data();
+  std::vector<std::vector<uint32_t>> offs(levels);
+  std::vector<std::vector<Affine<F>>> lvl_pts(levels);
+  for (int l = 1; l <= levels; l++) {
+    std::vector<uint32_t>& off = offs[l - 1];
+    off.resize(nbuckets + 1);
+    uint32_t run = 0;
+    for (uint64_t i = 0; i < nbuckets; i++) { off[i] = run; run += scan_value(counts[i], 1 << l); }
+    off[nbuckets] = run;
+    lvl_pts[l - 1].resize(run + 1);
+    std::vector<F> prefix(run + 1), totals(run / AFF_K + 2);
+    AffLevel<F> lv{seg_sorted, seg_pts, seg_off, off.data(), nbuckets, lvl_pts[l - 1].data(), prefix.data(), totals.data()};
+    const uint64_t nthreads = ((uint64_t)run + AFF_K - 1) / AFF_K;
+    for (uint64_t t = 0; t < nthreads; t++) aff_forward_thread<F>(lv, t);
+    for (uint64_t t = 0; t < nthreads; t++) totals[t] = F::inv(totals[t]);  // device: aff_invert (shared inversions)
+    for (uint64_t t = 0; t < nthreads; t++) aff_backward_thread<F>(lv, t);
+    seg_sorted = nullptr;
+    seg_pts = lvl_pts[l - 1].data();
+    seg_off = off.data();
+  }
   // tasks ordered by descending length (msm_task_hist / msm_task_place)
   std::vector<uint32_t> hist(MSM_MAX_CHUNK + 2, 0), hist_start(MSM_MAX_CHUNK + 1), hcur(MSM_MAX_CHUNK + 1, 0);
-  for (uint64_t i = 0; i < nbuckets; i++) msm_task_hist_thread(chunk, starts.data(), task_first.data(), hist.data(), i);
+  for (uint64_t i = 0; i < nbuckets; i++) msm_task_hist_thread(chunk, seg_off, task_first.data(), hist.data(), i);
   uint32_t run = 0;
   for (int i = 0; i <= MSM_MAX_CHUNK; i++) { hist_start[i] = run; run += hist[i]; }
   if (run != b) return -2;
   std::vector<MsmTask> tasks(b + 1);
   std::vector<MsmSlotSeg> slot_seg(b + 1);
   for (uint64_t i = 0; i < nbuckets; i++)
-    msm_task_place_thread(chunk, starts.data(), task_first.data(), hist_start.data(), hcur.data(), tasks.data(), slot_seg.data(), i);
+    msm_task_place_thread(chunk, seg_off, task_first.data(), hist_start.data(), hcur.data(), tasks.data(), slot_seg.data(), i);
   for (uint32_t t = 1; t < b; t++) if (tasks[t].len > tasks[t - 1].len) return -3;
   std::vector<XYZZ<F>> partial(b + 1);
   for (uint32_t t = 0; t < b; t++)
-    msm_accumulate_thread<F>(tasks.data(), sorted.data(), precomp ? table.data() : bases.data(), partial.data(), t);
+    msm_accumulate_thread<F>(tasks.data(), seg_sorted, seg_pts, partial.data(), t);
   for (uint64_t i = 0; i < nbuckets; i++) msm_fold_thread<F>(task_first.data(), partial.data(), i);
   // 2-D bucket reduction (ctx.cuh::enqueue_msm with loops in place of launches)
-  (void)bpc;
   const uint64_t groups = sh.total_groups();
   const int h = (sh.c - 1) / 2;
   const uint64_t Cn = 1ull << h, R = (uint64_t)sh.nb / Cn;

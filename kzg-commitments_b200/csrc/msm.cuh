@@ -294,7 +294,7 @@ KZG_HD void msm_accumulate_thread(const MsmTask* tasks, const uint32_t* sorted, 
   const MsmTask t = tasks[i];
   XYZZ<F> acc = XYZZ<F>::inf();
   for (uint32_t e = t.first; e < t.first + t.len; e++) {
-    const uint32_t rec = sorted[e];
+    const uint32_t rec = sorted ? sorted[e] : e;  // no record array: the points were pre-reduced (msm_affine.cuh)
     const Affine<F> p = bases[rec & 0x7fffffffu];
     acc.madd(p, (rec >> 31) != 0);
   }

@@ -301,3 +301,50 @@ def test_quotient_many_roots_systolic(ctxs, cname):
     P = kzg_b200.Poly(ctx, coeffs)
     q, _, _ = C.poly_quotient(coeffs, 2, 600)
     assert ts.create_proof(P, 2, 600).serialize() == C.serialize_g1(C.mul(C.poly_eval(q, s), C.g1))
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_batched_affine_levels(ctxs, cname):
+    """Forced batched-affine pre-reduction (msm_affine.cuh) at 1-4 levels: same bytes as the XYZZ-only path and
+    as the oracle, including a degenerate SRS (every base equal: P + P and P + (-P) inside the affine levels),
+    zero scalars and a batch."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(31 + C.id)
+    s = rng.randrange(C.r)
+    n = 3000
+    try:
+        for pre in (0, 2):
+            ctx.set_option("precompute", pre)
+            ctx.set_option("affine_levels", 0)
+            ctx.setup_powers(s, n, want_bytes=False)
+            sc = [rng.randrange(C.r) for _ in range(n)]
+            sc[5] = 0
+            raw = C.scalars_to_bytes(sc)
+            want = C.g1_to_octet(C.mul(C.poly_eval(sc, s), C.g1))[1:]
+            for lv in (0, 1, 2, 3, 4):
+                ctx.set_option("affine_levels", lv)
+                xy, inf = ctx.msm_g1(raw, n)
+                assert xy == want and not inf, (pre, lv)
+            ctx.set_option("affine_levels", 2)
+            out, infs = ctx.msm_g1_batch(raw[:2 * 1000 * ctx.SB], 1000, 2)
+            for b in range(2):
+                part = sc[b * 1000:(b + 1) * 1000]
+                assert out[b * 2 * ctx.M:(b + 1) * 2 * ctx.M] == C.g1_to_octet(C.mul(C.poly_eval(part, s), C.g1))[1:]
+        # degenerate SRS (s = 1): all bases are the generator
+        ctx.set_option("precompute", 0)
+        ctx.setup_powers(1, 64, want_bytes=False)
+        for lv in (1, 2, 3):
+            ctx.set_option("affine_levels", lv)
+            ctx.set_option("window_bits", 4)
+            sc = [5] * 20 + [C.r - 5] * 20 + [3] * 10
+            xy, inf = ctx.msm_g1(C.scalars_to_bytes(sc), len(sc))
+            assert xy == C.g1_to_octet(C.mul(30, C.g1))[1:], lv
+            xy, inf = ctx.msm_g1(C.scalars_to_bytes([9] * 8 + [C.r - 9] * 8), 16)
+            assert inf and xy == bytes(2 * ctx.M), lv
+            xy, inf = ctx.msm_g1(C.scalars_to_bytes([7] * 33), 33)
+            assert xy == C.g1_to_octet(C.mul(7 * 33, C.g1))[1:], lv
+    finally:
+        ctx.set_option("affine_levels", -1)
+        ctx.set_option("window_bits", 0)
+        ctx.set_option("precompute", 2)

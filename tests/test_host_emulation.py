@@ -94,7 +94,7 @@ def test_msm_pipeline_matches_reference_commits(hc, cname):
         n = len(coeffs) // C.SB
         if n == 0:
             continue
-        for c, chunk, bpc, precomp in ((4, 3, 2, 0), (5, 64, 16, 0), (6, 2, 4, 1)):
+        for c, chunk, bpc, precomp in ((4, 3, 2, 0), (5, 64, 0, 0), (6, 2, 1, 1)):  # bpc = affine pre-reduction levels
             raw, inf = _run(hc, C, 1, g1, coeffs, n, c=c, chunk=chunk, bpc=bpc, precomp=precomp)
             want = bytes.fromhex(case["commit"])[5:]
             assert raw == want, (cname, case["name"], c, precomp)
@@ -123,14 +123,14 @@ def test_msm_pipeline_edges(hc, cname):
         raw_sc = b"".join((s % (1 << (8 * C.SB))).to_bytes(C.SB, "little") for s in sc)
         want = C.msm([s % C.r for s in sc], pts)
         for c, precomp in ((4, 0), (7, 0), (5, 1)):
-            raw, inf = _run(hc, C, 1, pts, raw_sc, len(sc), c=c, chunk=2, bpc=4, precomp=precomp)
+            raw, inf = _run(hc, C, 1, pts, raw_sc, len(sc), c=c, chunk=2, bpc=3, precomp=precomp)
             assert raw == C.g1_to_octet(want)[1:], (sc, c, precomp)
             assert inf[0] == int(want is None)
     # base_offset and batch: two MSMs over a sub-range
     kat, srs = load(cname)
     g1, _ = C.srs_from_file_bytes(srs)
     sc = [rng.randrange(C.r) for _ in range(2 * 9)]
-    raw, inf = _run(hc, C, 1, g1, C.scalars_to_bytes(sc), 9, base_offset=0, batch=2, c=5, chunk=4, bpc=8)
+    raw, inf = _run(hc, C, 1, g1, C.scalars_to_bytes(sc), 9, base_offset=0, batch=2, c=5, chunk=4, bpc=1)
     for b in range(2):
         want = C.msm(sc[9 * b:9 * b + 9], g1[:9])
         assert raw[b * 2 * C.M:(b + 1) * 2 * C.M] == C.g1_to_octet(want)[1:]
