@@ -195,6 +195,7 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep rank 0's stdout to the one JSON line
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -220,8 +221,7 @@ def run_b200(args):
 
     def fold_partials():
         """N > 1: all-gather the projective partial sums (NCCL) and fold them on every rank."""
-        parts = sharding.gather_partials(dist, ctx.msm_fetch_partial(), device=torch.device("cuda", local))
-        return ctx.g1_sum_partials(parts)
+        return sharding.gather_partials_device(dist, ctx, torch.device("cuda", local))
 
     def step_resident():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

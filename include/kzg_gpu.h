@@ -97,6 +97,13 @@ int kzg_gpu_msm_fetch_partial(kzg_gpu_ctx* ctx, uint32_t* xyzz_words, size_t* n_
 int kzg_gpu_g1_sum_partials(kzg_gpu_ctx* ctx, const uint32_t* xyzz_words, uint64_t n_partials,
                             uint8_t* out_xy /* 2M */, int* is_inf);
 
+/* Device-resident forms of the two calls above for an NCCL exchange without host round trips: the device
+ * address and byte size of the most recent single launch's projective result, and the fold of n_partials
+ * such records lying contiguously in DEVICE memory (e.g. the output of ncclAllGather). */
+int kzg_gpu_msm_partial_device(kzg_gpu_ctx* ctx, void** d_ptr, size_t* bytes);
+int kzg_gpu_g1_sum_partials_device(kzg_gpu_ctx* ctx, const void* d_xyzz, uint64_t n_partials,
+                                   uint8_t* out_xy /* 2M */, int* is_inf);
+
 /* q = P div prod_{j<k} (x - (first_root + j)): coeffs n*SB bytes in, (n-k)*SB bytes out (k < n). */
 int kzg_gpu_poly_quotient(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k,
                           uint8_t* q_out);

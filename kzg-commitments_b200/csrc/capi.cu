@@ -100,6 +100,12 @@ int kzg_gpu_msm_fetch_partial(kzg_gpu_ctx* ctx, uint32_t* words, size_t* n_words
 int kzg_gpu_g1_sum_partials(kzg_gpu_ctx* ctx, const uint32_t* words, uint64_t n, uint8_t* out_xy, int* is_inf) {
   return ctx ? ctx->sum_partials(words, n, out_xy, is_inf) : KZG_GPU_ERR_ARG;
 }
+int kzg_gpu_msm_partial_device(kzg_gpu_ctx* ctx, void** d_ptr, size_t* bytes) {
+  return ctx ? ctx->partial_device(d_ptr, bytes) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_g1_sum_partials_device(kzg_gpu_ctx* ctx, const void* d_words, uint64_t n, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->sum_partials_device(d_words, n, out_xy, is_inf) : KZG_GPU_ERR_ARG;
+}
 int kzg_gpu_poly_quotient(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) {
   return ctx ? ctx->poly_quotient(coeffs, n, first_root, k, q_out) : KZG_GPU_ERR_ARG;
 }

@@ -77,6 +77,8 @@ struct kzg_gpu_ctx {
   virtual int fetch(uint8_t* out, int* is_inf) = 0;
   virtual int fetch_partial(uint32_t* words, size_t* n_words) = 0;
   virtual int sum_partials(const uint32_t* words, uint64_t n, uint8_t* out, int* is_inf) = 0;
+  virtual int partial_device(void** d_ptr, size_t* bytes) = 0;
+  virtual int sum_partials_device(const void* d_words, uint64_t n, uint8_t* out, int* is_inf) = 0;
   virtual int poly_quotient(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) = 0;
   virtual int poly_eval(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* y_out) = 0;
   virtual int prove(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out, int* is_inf) = 0;
@@ -499,6 +501,27 @@ struct Ctx final : kzg_gpu_ctx {
     CK(cudaMemcpyAsync(words, out_xyzz.p, sizeof(XYZZ<Fp>), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
     return KZG_GPU_OK;
+  }
+  // device-resident variants for the NCCL path: the partial never visits the host
+  int partial_device(void** d_ptr, size_t* bytes) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    if (!d_ptr || !bytes) return KZG_GPU_ERR_ARG;
+    if (last_batch != 1 || last_group != 1 || !out_xyzz.p) return KZG_GPU_ERR_STATE;
+    *d_ptr = out_xyzz.p;
+    *bytes = sizeof(XYZZ<Fp>);
+    return KZG_GPU_OK;
+  }
+  int sum_partials_device(const void* d_words, uint64_t n, uint8_t* out, int* is_inf) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!d_words || n == 0 || n > 4096) return KZG_GPU_ERR_ARG;
+    CK(out_bytes.ensure(4 * M));
+    CK(out_inf.ensure(sizeof(int)));
+    sum_points<Fp><<<1, 1, 0, stream>>>(n, static_cast<const XYZZ<Fp>*>(d_words), out_bytes.as<uint8_t>(), out_inf.as<int>(), M);
+    LAUNCHED();
+    last_batch = 1;
+    last_group = 1;
+    return fetch_locked(out, is_inf);
   }
   int sum_partials(const uint32_t* words, uint64_t n, uint8_t* out, int* is_inf) override {
     std::lock_guard<std::recursive_mutex> lock(mu);

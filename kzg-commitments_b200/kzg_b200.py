@@ -63,6 +63,8 @@ def load_library():
         "kzg_gpu_msm_fetch": (ctypes.c_int, [vp, u8p, ip]),
         "kzg_gpu_msm_fetch_partial": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_uint32), ctypes.POINTER(ctypes.c_size_t)]),
         "kzg_gpu_g1_sum_partials": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_uint32), u64, u8p, ip]),
+        "kzg_gpu_msm_partial_device": (ctypes.c_int, [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]),
+        "kzg_gpu_g1_sum_partials_device": (ctypes.c_int, [vp, vp, u64, u8p, ip]),
         "kzg_gpu_poly_quotient": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
         "kzg_gpu_poly_eval_range": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
         "kzg_gpu_prove": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p, ip]),
@@ -87,7 +89,7 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_msm_g2", "kzg_gpu_msm_g1_batch", "kzg_gpu_msm_g1_launch", "kzg_gpu_msm_fetch",
     "kzg_gpu_msm_fetch_partial", "kzg_gpu_g1_sum_partials", "kzg_gpu_poly_quotient", "kzg_gpu_poly_eval_range",
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
-    "kzg_gpu_phase_times", "kzg_gpu_msm_stats",
+    "kzg_gpu_phase_times", "kzg_gpu_msm_stats", "kzg_gpu_msm_partial_device", "kzg_gpu_g1_sum_partials_device",
 ]
 
 
@@ -194,6 +196,18 @@ class Context:
         words = (ctypes.c_uint32 * nw.value)()
         self._check(self.lib.kzg_gpu_msm_fetch_partial(self.h, words, ctypes.byref(nw)), "fetch_partial")
         return bytes(words)
+
+    def msm_partial_device(self):
+        """(device address, bytes) of the projective result of the most recent single G1 launch."""
+        p, nb = ctypes.c_void_p(), ctypes.c_size_t(0)
+        self._check(self.lib.kzg_gpu_msm_partial_device(self.h, ctypes.byref(p), ctypes.byref(nb)), "msm_partial_device")
+        return p.value, nb.value
+
+    def g1_sum_partials_device(self, d_ptr, n):
+        out = ctypes.create_string_buffer(2 * self.M)
+        inf = ctypes.c_int(0)
+        self._check(self.lib.kzg_gpu_g1_sum_partials_device(self.h, _ptr(d_ptr), n, out, ctypes.byref(inf)), "g1_sum_partials_device")
+        return out.raw, bool(inf.value)
 
     def g1_sum_partials(self, partials):
         raw = b"".join(partials)

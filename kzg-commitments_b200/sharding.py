@@ -29,3 +29,23 @@ def gather_partials(dist, partial_bytes, device=None):
     out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
     dist.all_gather(out, t)
     return [bytes(o.cpu().numpy().tobytes()) for o in out]
+
+
+class _DevBytes:
+    """A raw device allocation presented through __cuda_array_interface__ so torch can wrap it without a copy."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def gather_partials_device(dist, ctx, device):
+    """NCCL all-gather of this rank's projective partial straight from the context's device buffer, then the fold
+    on the device (kzg_gpu_g1_sum_partials_device).  The caller has already waited for the MSM on ctx.stream."""
+    import torch
+    ptr, nb = ctx.msm_partial_device()
+    mine = torch.as_tensor(_DevBytes(ptr, nb), device=device)
+    world = dist.get_world_size()
+    allp = torch.empty(world * nb, dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(allp, mine)
+    torch.cuda.current_stream(device).synchronize()
+    return ctx.g1_sum_partials_device(allp, world)

@@ -246,6 +246,20 @@ def test_batch_and_point_range_split(ctxs):
         partials.append(ctx.msm_fetch_partial())
     xy, inf = ctx.g1_sum_partials(partials)
     assert xy == full and not inf
+    # the same fold with the partials lying in device memory (what the NCCL all-gather leaves behind)
+    import torch
+    import sharding
+    dev = []
+    for g in range(4):
+        lo, hi = g * n // 4, (g + 1) * n // 4
+        ctx.msm_g1(C.scalars_to_bytes(blobs[0][lo:hi]), hi - lo, base_offset=lo)
+        ptr, nb = ctx.msm_partial_device()
+        assert nb == len(partials[g])
+        dev.append(torch.as_tensor(sharding._DevBytes(ptr, nb), device="cuda").clone())
+    allp = torch.cat(dev)
+    torch.cuda.synchronize()
+    xy, inf = ctx.g1_sum_partials_device(allp, 4)
+    assert xy == full and not inf
 
 
 def test_msm_2_16_linearity_and_oracle(ctxs):
