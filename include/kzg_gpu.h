@@ -13,6 +13,7 @@
  *   kzg_gpu_poly_quotient          ZZ_pX q = (P - I) / Z          src/trusted_setup.cpp:218-225
  *   kzg_gpu_poly_eval_range        evaluate_polynomial_points     src/util.cpp:186-211
  *   kzg_gpu_prove                  create_proof body              src/trusted_setup.cpp:214-228
+ *   kzg_gpu_interpolate_range      polyfit / linear_roots_and_polyfit   src/util.cpp:172-184 (consecutive nodes)
  *   kzg_gpu_setup_powers           trusted_setup(int) + generate_elements_range
  *                                                                 src/trusted_setup.cpp:21-74, 123-135
  *   kzg_gpu_srs_load               the _G1/_G2 vectors a trusted_setup holds (src/kzg.h:183-185),
@@ -114,6 +115,14 @@ int kzg_gpu_poly_eval_range(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n,
  * k >= n gives the zero quotient, i.e. the point at infinity (benchmark "Proofs: 4096" row). */
 int kzg_gpu_prove(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k,
                   uint8_t* out_xy /* 2M */, int* is_inf);
+
+/* Interpolation through the k consecutive nodes x_i = first_x + i (what every kzg::blob holds, src/blob.cpp:20-48):
+ * replaces polyfit (src/util.cpp:180-184, used by poly::from_blob src/poly.cpp:4-6) and linear_roots_and_polyfit
+ * (src/util.cpp:172-178, used by verify_proof src/trusted_setup.cpp:239).  ys: k*SB bytes; coeffs_out: the k
+ * coefficients of the interpolant I (zero-padded, low degree first) or NULL; vanishing_out: the k+1 coefficients of
+ * Z = prod (x - x_i) or NULL. */
+int kzg_gpu_interpolate_range(kzg_gpu_ctx* ctx, const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out,
+                              uint8_t* vanishing_out);
 
 /* The context's CUDA stream (cudaStream_t) so a caller can time with events on it. */
 void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx);

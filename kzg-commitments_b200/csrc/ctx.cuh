@@ -82,6 +82,7 @@ struct kzg_gpu_ctx {
   virtual int poly_quotient(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) = 0;
   virtual int poly_eval(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* y_out) = 0;
   virtual int prove(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out, int* is_inf) = 0;
+  virtual int interpolate(const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out, uint8_t* vanish_out) = 0;
   virtual int microbench(int kind, double* ops) = 0;
   virtual int selftest(int* failures) = 0;
   virtual int phase_times(float* ms, int n) = 0;
@@ -128,7 +129,8 @@ struct Ctx final : kzg_gpu_ctx {
   // scratch
   DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
       out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3, aff_off, aff_a, aff_b, aff_prefix,
-      aff_totals;
+      aff_totals, inv_fact, it_u, it_pa, it_pb, it_za, it_zb;
+  uint64_t inv_fact_n = 0;
   // description of the most recent launch, for fetch()
   uint64_t last_batch = 0;
   int last_group = 1;
@@ -137,7 +139,7 @@ struct Ctx final : kzg_gpu_ctx {
     cudaSetDevice(device);
     for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
-                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &red0, &red1, &red2, &red3})
+                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
     for (cudaEvent_t e : phase_ev) if (e) cudaEventDestroy(e);
     if (stream) cudaStreamDestroy(stream);
@@ -632,6 +634,57 @@ struct Ctx final : kzg_gpu_ctx {
     if (rc) return rc;
     // same stream: the MSM is ordered after the quotient; qbytes is not touched by the MSM path
     return msm(1, qbytes.as<uint8_t>(), true, n - k, 1, 0, out, is_inf, true);
+  }
+
+  // interpolation through the consecutive nodes first_x .. first_x + k - 1 (polyfit / linear_roots_and_polyfit)
+  int interpolate(const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out, uint8_t* vanish_out) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!ys || k == 0 || k > (1ull << 22) || (!coeffs_out && !vanish_out)) return KZG_GPU_ERR_ARG;
+    uint64_t kp = 1;
+    while (kp < k) kp <<= 1;
+    if (inv_fact_n < k) {  // 1/t! table, cached
+      const uint64_t want = std::max<uint64_t>(kp, 4096);
+      CK(inv_fact.ensure(want * sizeof(Fr)));
+      fr_inv_factorials<C><<<1, 32, 0, stream>>>((uint32_t)want, inv_fact.as<Fr>());
+      LAUNCHED();
+      inv_fact_n = want;
+    }
+    CK(stage.ensure(k * (size_t)SB));
+    CK(it_u.ensure(k * sizeof(Fr)));
+    CK(it_pa.ensure(kp * sizeof(Fr)));
+    CK(it_pb.ensure(kp * sizeof(Fr)));
+    CK(it_za.ensure(2 * kp * sizeof(Fr)));
+    CK(it_zb.ensure(2 * kp * sizeof(Fr)));
+    CK(qbytes.ensure((kp + 1) * (size_t)SB));
+    CK(cudaMemcpyAsync(stage.p, ys, k * (size_t)SB, cudaMemcpyHostToDevice, stream));
+    interp_scale_values<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(
+        k, stage.as<uint8_t>(), inv_fact.as<Fr>(), it_u.as<Fr>());
+    LAUNCHED();
+    Fr *pin = it_pa.as<Fr>(), *pout = it_pb.as<Fr>(), *zin = it_za.as<Fr>(), *zout = it_zb.as<Fr>();
+    interp_leaves<C><<<(unsigned)std::min<uint64_t>((kp + 3) / 4, 148 * 16), 128, 0, stream>>>(
+        k, kp, (long long)first_x, it_u.as<Fr>(), inv_fact.as<Fr>(), pin, zin);
+    LAUNCHED();
+    for (uint64_t m = 1; m < kp; m <<= 1) {
+      const uint64_t npairs = kp / (2 * m), warps = npairs * (4 * m + 1);
+      interp_tree_level<C><<<(unsigned)std::min<uint64_t>((warps + 3) / 4, 148 * 32), 128, 0, stream>>>(m, npairs, pin, zin, pout, zout);
+      LAUNCHED();
+      std::swap(pin, pout);
+      std::swap(zin, zout);
+    }
+    if (coeffs_out) {
+      fr_to_bytes<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(k, pin, qbytes.as<uint8_t>());
+      LAUNCHED();
+      CK(cudaMemcpyAsync(coeffs_out, qbytes.p, k * (size_t)SB, cudaMemcpyDeviceToHost, stream));
+      CK(cudaStreamSynchronize(stream));
+    }
+    if (vanish_out) {
+      fr_to_bytes<C><<<(unsigned)std::min<uint64_t>((k + 128) / 128, 148 * 8), 128, 0, stream>>>(k + 1, zin, qbytes.as<uint8_t>());
+      LAUNCHED();
+      CK(cudaMemcpyAsync(vanish_out, qbytes.p, (k + 1) * (size_t)SB, cudaMemcpyDeviceToHost, stream));
+      CK(cudaStreamSynchronize(stream));
+    }
+    return KZG_GPU_OK;
   }
 
   // ------------------------------------------------------------------ trusted setup

@@ -192,4 +192,123 @@ poly_eval_range_kernel(uint64_t n, long long first_root, uint64_t k, const Field
   }
 }
 
+
+// ======================================================================================================
+// Interpolation through consecutive integer nodes x_i = first_x + i: replaces
+//   polyfit / linear_roots_and_polyfit   src/util.cpp:172-184, 213-248, 269-284   (subproduct tree over NTL mul)
+// for the node sets this library's blobs always have (blob::from_bytes / from_string number their chunks
+// consecutively, src/blob.cpp:20-48).  Same polynomial, so same canonical coefficients, computed as
+//   1. Newton coefficients  c_j = Delta^j y_0 / j! = sum_{i<=j} (y_i / i!) * ((-1)^(j-i) / (j-i)!)
+//      — one triangular convolution, a warp per output;
+//   2. a product tree in the Newton basis: for a node range split into L | R,
+//          P = P_L + Z_L * P_R,   Z = Z_L * Z_R,   Z_L = prod_{t in L} (x - x_t),
+//      schoolbook products (no NTT: r - 1 has 2-adicity 2 on the BN curves), a warp per output coefficient,
+//      one launch per tree level.  The root holds I (first k coefficients) and Z (k + 1 coefficients).
+// k is padded to a power of two with c_j = 0, Z_j = 1 leaves, which changes neither I nor Z.
+
+// inv_fact[t] = 1 / t!  for t < n  (Montgomery).  One thread; cached by the context (a few ms once for n = 4096).
+template <class C>
+__global__ void fr_inv_factorials(uint32_t n, Field<typename C::FrP>* __restrict__ inv_fact) {
+  using Fr = Field<typename C::FrP>;
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  const Fr one = Fr::one();
+  Fr f = one, t = one;  // f = i!, t = i (Montgomery)
+  for (uint32_t i = 1; i < n; i++) {
+    if (i > 1) t = Fr::add(t, one);
+    f = Fr::mul(f, t);
+  }
+  Fr inv = Fr::inv(f);  // 1 / (n-1)!
+  for (uint32_t i = n; i-- > 0;) {
+    inv_fact[i] = inv;
+    inv = Fr::mul(inv, t);  // 1/(i-1)! = (1/i!) * i
+    t = Fr::sub(t, one);
+  }
+}
+
+template <class Fr>
+__device__ __forceinline__ Fr warp_sum_field(Fr v) {
+  for (int d = 16; d > 0; d >>= 1) {
+    Fr o;
+#pragma unroll
+    for (int i = 0; i < Fr::L; i++) o.v[i] = __shfl_down_sync(0xffffffffu, v.v[i], d);
+    v = Fr::add(v, o);
+  }
+  return v;  // lane 0 holds the sum
+}
+
+// u_i = y_i / i!  (y from little-endian bytes)
+template <class C>
+__global__ void interp_scale_values(uint64_t k, const uint8_t* __restrict__ ys, const Field<typename C::FrP>* __restrict__ inv_fact,
+                                    Field<typename C::FrP>* __restrict__ u) {
+  using Fr = Field<typename C::FrP>;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < k; i += (uint64_t)gridDim.x * blockDim.x)
+    u[i] = Fr::mul(fr_load<C>(ys, i), inv_fact[i]);
+}
+
+// leaves of the product tree (level m = 1) for kp = padded k:
+//   P0[j] = c_j = sum_{i<=j} u_i * (-1)^(j-i) inv_fact[j-i]   (0 for j >= k)
+//   Z0[j] = (x - (first_x + j)) as 2 coefficients  [-(first_x+j), 1]   ([1, 0] for j >= k)
+template <class C>
+__global__ void __launch_bounds__(128)
+interp_leaves(uint64_t k, uint64_t kp, long long first_x, const Field<typename C::FrP>* __restrict__ u,
+              const Field<typename C::FrP>* __restrict__ inv_fact, Field<typename C::FrP>* __restrict__ P0,
+              Field<typename C::FrP>* __restrict__ Z0) {
+  using Fr = Field<typename C::FrP>;
+  const int lane = threadIdx.x & 31;
+  const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t j = warp; j < kp; j += nwarps) {
+    Fr acc = Fr::zero();
+    if (j < k) {
+      for (uint64_t i = lane; i <= j; i += 32) {
+        const Fr term = Fr::mul(u[i], inv_fact[j - i]);
+        acc = ((j - i) & 1) ? Fr::sub(acc, term) : Fr::add(acc, term);
+      }
+    }
+    acc = warp_sum_field<Fr>(acc);
+    if (lane == 0) {
+      P0[j] = acc;
+      if (j < k) {
+        Z0[2 * j] = Fr::neg(fr_from_i64<C>(first_x + (long long)j));
+        Z0[2 * j + 1] = Fr::one();
+      } else {
+        Z0[2 * j] = Fr::one();
+        Z0[2 * j + 1] = Fr::zero();
+      }
+    }
+  }
+}
+
+// One tree level: nodes of size m (P: m coefficients, Z: m + 1) are merged in pairs into nodes of size 2m.
+//   Pout[q][i] = (i < m ? P_L[i] : 0) + sum_t Z_L[t] * P_R[i - t],   i < 2m
+//   Zout[q][i] = sum_t Z_L[t] * Z_R[i - t],                           i <= 2m
+// A warp per output coefficient, lanes stride over t.
+template <class C>
+__global__ void __launch_bounds__(128)
+interp_tree_level(uint64_t m, uint64_t npairs, const Field<typename C::FrP>* __restrict__ Pin,
+                  const Field<typename C::FrP>* __restrict__ Zin, Field<typename C::FrP>* __restrict__ Pout,
+                  Field<typename C::FrP>* __restrict__ Zout) {
+  using Fr = Field<typename C::FrP>;
+  const int lane = threadIdx.x & 31;
+  const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const uint64_t per_pair = 4 * m + 1;  // 2m outputs of P, 2m + 1 of Z
+  for (uint64_t w = warp; w < npairs * per_pair; w += nwarps) {
+    const uint64_t q = w / per_pair, o = w - q * per_pair;
+    const bool is_z = o >= 2 * m;
+    const uint64_t i = is_z ? o - 2 * m : o;
+    const Fr* ZL = Zin + (2 * q) * (m + 1);
+    const Fr* R = is_z ? Zin + (2 * q + 1) * (m + 1) : Pin + (2 * q + 1) * m;
+    const uint64_t rlen = is_z ? m + 1 : m;
+    const uint64_t t_lo = i >= rlen ? i - rlen + 1 : 0, t_hi = i < m ? i : m;  // t in [t_lo, t_hi]
+    Fr acc = Fr::zero();
+    for (uint64_t t = t_lo + lane; t <= t_hi; t += 32) acc = Fr::add(acc, Fr::mul(ZL[t], R[i - t]));
+    acc = warp_sum_field<Fr>(acc);
+    if (lane == 0) {
+      if (is_z) Zout[q * (2 * m + 1) + i] = acc;
+      else Pout[q * (2 * m) + i] = (i < m) ? Fr::add(acc, Pin[(2 * q) * m + i]) : acc;
+    }
+  }
+}
+
 }  // namespace kzgb200

@@ -68,6 +68,7 @@ def load_library():
         "kzg_gpu_poly_quotient": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
         "kzg_gpu_poly_eval_range": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
         "kzg_gpu_prove": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p, ip]),
+        "kzg_gpu_interpolate_range": (ctypes.c_int, [vp, u8p, i64, u64, u8p, u8p]),
         "kzg_gpu_ctx_stream": (vp, [vp]),
         "kzg_gpu_launch_count": (u64, [vp]),
         "kzg_gpu_microbench": (ctypes.c_int, [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
@@ -90,6 +91,7 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_msm_fetch_partial", "kzg_gpu_g1_sum_partials", "kzg_gpu_poly_quotient", "kzg_gpu_poly_eval_range",
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
     "kzg_gpu_phase_times", "kzg_gpu_msm_stats", "kzg_gpu_msm_partial_device", "kzg_gpu_g1_sum_partials_device",
+    "kzg_gpu_interpolate_range",
 ]
 
 
@@ -230,6 +232,14 @@ class Context:
         self._check(self.lib.kzg_gpu_poly_eval_range(self.h, coeffs, n, first_root, k, out), "poly_eval_range")
         return out.raw
 
+    def interpolate_range(self, ys, first_x, want_vanishing=True):
+        """(I, Z) through the nodes first_x + i: I as k coefficient records, Z as k + 1 (or None)."""
+        k = len(ys) // self.SB
+        out = ctypes.create_string_buffer(k * self.SB)
+        van = ctypes.create_string_buffer((k + 1) * self.SB) if want_vanishing else None
+        self._check(self.lib.kzg_gpu_interpolate_range(self.h, ys, first_x, k, out, van), "interpolate_range")
+        return out.raw, (van.raw if want_vanishing else None)
+
     def prove(self, coeffs, first_root, k):
         n = len(coeffs) // self.SB
         out = ctypes.create_string_buffer(2 * self.M)
@@ -293,6 +303,14 @@ class Poly:
     @property
     def degree(self):
         return len(self.coeffs) - 1
+
+    @classmethod
+    def from_blob(cls, ctx, ys, offset=0):
+        """poly::from_blob (src/poly.cpp:4-6 -> polyfit, src/util.cpp:180-184) for a blob whose chunk i sits at
+        x = offset + i (blob::from_bytes / from_string): interpolation on the device."""
+        raw = ys if isinstance(ys, (bytes, bytearray)) else b"".join((int(v) % ctx.r).to_bytes(ctx.SB, "little") for v in ys)
+        coeffs, _ = ctx.interpolate_range(bytes(raw), offset, want_vanishing=False)
+        return cls(ctx, coeffs)
 
     def serialize(self):
         """serialize_ZZ_pX (src/util.cpp:118-144): int64 degree | per coefficient [u8 nbytes | LE magnitude]."""

@@ -1,7 +1,7 @@
 #!/usr/bin/env bash
 # src/build_dropin.sh — builds the kzg.h drop-in: the reference's UNMODIFIED headers and its unmodified
-# blob/poly/commit/proof/util sources (compiled where they lie under /root/reference) + OUR
-# src/trusted_setup_gpu.cpp in place of the reference's src/trusted_setup.cpp, linked against
+# blob/commit/proof/util sources (compiled where they lie under /root/reference) + OUR
+# src/trusted_setup_gpu.cpp and src/poly_gpu.cpp in place of the reference's src/trusted_setup.cpp and src/poly.cpp, linked against
 # kzg-commitments_b200/libkzg_gpu.so.  Then links the reference's own callers against it, unchanged:
 #   oracle/_ref/dropin/testing-bn254-gpu        testing/testing.cpp   (36 property checks)
 #   oracle/_ref/dropin/benchmark-<curve>-gpu    benchmark/benchmark.cpp
@@ -25,10 +25,12 @@ build_curve() {
   local c=$1 inc=$SCR/include-$1 obj=$SCR/dropin-obj-$1
   mkdir -p "$obj"
   local I="-I$inc -I$SCR/ntl/include -I$REF/src"
-  for f in blob poly commit proof util; do
+  for f in blob commit proof util; do
     g++ -O2 $I -c "$REF/src/$f.cpp" -o "$obj/$f.o"
   done
+  rm -f "$obj/poly.o"
   g++ -O2 -std=c++17 $I -c "$HERE/trusted_setup_gpu.cpp" -o "$obj/trusted_setup_gpu.o"
+  g++ -O2 -std=c++17 $I -c "$HERE/poly_gpu.cpp" -o "$obj/poly_gpu.o"
   rm -f "$OUT/libkzg-$c-gpu.a"; ar rcs "$OUT/libkzg-$c-gpu.a" "$obj"/*.o
   local L="$OUT/libkzg-$c-gpu.a $SCR/miracl/core.a $SCR/ntl/src/ntl.a -L$PKG -lkzg_gpu -lpthread -Wl,-rpath,\$ORIGIN/../../../kzg-commitments_b200"
   g++ -O2 $I "$ROOT/oracle/ref_harness.cpp" $L -o "$OUT/kzgdrop-$c"

@@ -9,9 +9,10 @@
 //   create_proof [src/trusted_setup.cpp:214-228]   -> kzg_gpu_prove       (quotient + MSM chained on device;
 //                                                     (P - I)/Z == P div Z, so neither I nor the evaluations are needed)
 //   trusted_setup(int) [src/trusted_setup.cpp:21-74, 123-135] -> kzg_gpu_setup_powers (fixed-base batch)
-// What does not change: argument checks and exception types/messages, the SRS file format, the host-side
-// interpolation of verify_proof (util.cpp linear_roots_and_polyfit) and the two pairings
-// (PAIR_ate / PAIR_fexp, src/trusted_setup.cpp:242-253), which stay MIRACL host code by design.
+// What does not change: argument checks and exception types/messages, the SRS file format and the two pairings
+// (PAIR_ate / PAIR_fexp, src/trusted_setup.cpp:242-253), which stay MIRACL host code by design.  verify_proof's
+// interpolation (linear_roots_and_polyfit, util.cpp:172-178) runs on the device for consecutive nodes
+// (kzg_gpu_interpolate_range) and keeps the reference's host routine for hand-built blobs with arbitrary x.
 // There is no CPU fallback: a failing C-ABI call (no GPU, out of memory) throws std::runtime_error.
 //
 // kzg.h gives trusted_setup no spare member and no destructor, so the device context of a setup lives in
@@ -28,6 +29,7 @@
 #include <string>
 #include <vector>
 
+#include "gpu_side.h"
 #include "util.h"
 #include "../include/kzg_gpu.h"
 
@@ -155,6 +157,51 @@ kzg_gpu_ctx* device_of(const void* self, std::vector<ECP>& g1, std::vector<ECP2>
 }
 
 }  // namespace
+
+// ---- shared with poly_gpu.cpp (gpu_side.h)
+kzg_gpu_ctx* kzg_b200::poly_ctx() {
+  static std::mutex mu;
+  static kzg_gpu_ctx* ctx = nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ctx) ctx = new_ctx();
+  return ctx;
+}
+
+bool kzg_b200::consecutive_nodes(const std::vector<std::pair<NTL::ZZ_p, NTL::ZZ_p>>& points, int64_t& first_x,
+                                 std::vector<uint8_t>& ys) {
+  if (points.empty()) return false;
+  const ZZ& x0 = rep(points[0].first);
+  if (NumBits(x0) > 62) return false;
+  first_x = (int64_t)conv<long>(x0);
+  const int SB = kzg::CURVE_ORDER_BYTES;
+  ys.assign(points.size() * (size_t)SB, 0);
+  for (size_t i = 0; i < points.size(); i++) {
+    const ZZ& xi = rep(points[i].first);
+    if (NumBits(xi) > 62 || (int64_t)conv<long>(xi) != first_x + (int64_t)i) return false;
+    BytesFromZZ(ys.data() + i * SB, rep(points[i].second), SB);
+  }
+  return true;
+}
+
+void kzg_b200::interpolate_consecutive(int64_t first_x, const std::vector<uint8_t>& ys, NTL::ZZ_pX* I, NTL::ZZ_pX* Z) {
+  const int SB = kzg::CURVE_ORDER_BYTES;
+  const size_t k = ys.size() / SB;
+  std::vector<uint8_t> ci(I ? k * SB : 0), cz(Z ? (k + 1) * SB : 0);
+  kzg_gpu_ctx* ctx = poly_ctx();
+  int rc = kzg_gpu_interpolate_range(ctx, ys.data(), first_x, k, I ? ci.data() : nullptr, Z ? cz.data() : nullptr);
+  if (rc) fail(ctx, rc, "interpolate_range");
+  auto unpack = [&](const std::vector<uint8_t>& raw, size_t n, NTL::ZZ_pX& out) {
+    out.SetLength((long)n);
+    ZZ z;
+    for (size_t i = 0; i < n; i++) {
+      ZZFromBytes(z, raw.data() + i * SB, SB);
+      conv(out[(long)i], z);
+    }
+    out.normalize();
+  };
+  if (I) unpack(ci, k, *I);
+  if (Z) unpack(cz, k + 1, *Z);
+}
 
 // ------------------------------------------------------------------------------------------------
 void kzg::init() {  // same contract as the reference: NTL modulus = group order, CURVE_ORDER_BYTES = its byte length
@@ -293,7 +340,12 @@ bool kzg::trusted_setup::verify_proof(kzg::commit& commit, kzg::proof& proof, kz
   if (points.size() >= _G1.size()) return false;
 
   ZZ_pX interp, vanish;
-  linear_roots_and_polyfit(interp, vanish, points);  // host NTL, as in the reference (SURVEY 8(f) N1 moves it)
+  int64_t first_x = 0;
+  std::vector<uint8_t> ys;
+  if (kzg_b200::consecutive_nodes(points, first_x, ys))
+    kzg_b200::interpolate_consecutive(first_x, ys, &interp, &vanish);  // device
+  else
+    linear_roots_and_polyfit(interp, vanish, points);                  // arbitrary nodes: the reference's host routine
 
   ECP2 z_s = polyeval_G2(vanish);                     // device
   ECP i_s = polyeval_G1(interp);                      // device

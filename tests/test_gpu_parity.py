@@ -362,3 +362,36 @@ def test_batched_affine_levels(ctxs, cname):
         ctx.set_option("affine_levels", -1)
         ctx.set_option("window_bits", 0)
         ctx.set_option("precompute", 2)
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_interpolation_matches_reference_and_round_trips(ctxs, cname):
+    """kzg_gpu_interpolate_range against the reference's linear_roots_and_polyfit outputs stored
+    in the golden vectors (I and Z for every opening), against the oracle's Lagrange interpolation, and — at the
+    sizes the benchmark uses — through the round trip  evaluate(interpolate(ys)) == ys  and  Z(x_i) == 0."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    kat, _ = load(cname)
+    checked = 0
+    for case in kat["cases"]:
+        for op in case["openings"]:
+            ys = bytes.fromhex(op["ys"])
+            I, Z = ctx.interpolate_range(ys, op["off"])
+            assert I.hex() == op["interp"], (case["name"], op["off"], op["k"])
+            assert Z.hex() == op["vanishing"], (case["name"], op["off"], op["k"])
+            checked += 1
+    assert checked > 50
+    rng = random.Random(11 + C.id)
+    for off, k in ((0, 1), (7, 2), (0, 3), (5, 33), (100, 64)):
+        ys = [rng.randrange(C.r) for _ in range(k)]
+        I, Z = ctx.interpolate_range(C.scalars_to_bytes(ys), off)
+        assert I == C.scalars_to_bytes((C.interpolate([off + i for i in range(k)], ys) + [0] * k)[:k]), (off, k)
+        assert Z == C.scalars_to_bytes(C.vanishing_poly(off, k)), (off, k)
+    for off, k in ((0, 4096), (3, 4229), (1, 1000)):
+        ys = C.scalars_to_bytes([rng.randrange(C.r) for _ in range(k)])
+        I, Z = ctx.interpolate_range(ys, off)
+        assert ctx.poly_eval_range(I, off, k) == ys, (off, k)
+        assert ctx.poly_eval_range(Z, off, k) == bytes(len(ys)), (off, k)
+        assert Z[-ctx.SB:] == (1).to_bytes(ctx.SB, "little")
+    P = kzg_b200.Poly.from_blob(ctx, [ord(ch) for ch in "hello there my name is bob"])
+    assert P.coeffs == C.poly_trim(C.interpolate(list(range(26)), [ord(ch) for ch in "hello there my name is bob"]))
