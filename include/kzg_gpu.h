@@ -116,6 +116,11 @@ int kzg_gpu_poly_eval_range(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n,
 int kzg_gpu_prove(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k,
                   uint8_t* out_xy /* 2M */, int* is_inf);
 
+/* `batch` independent create_proof calls in one: polynomial b = coeffs + b*n*SB (n coefficients each, zero-padded),
+ * opened at the k consecutive points first_roots[b] .. first_roots[b]+k-1.  out_xy: batch*2M bytes. */
+int kzg_gpu_prove_batch(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, const int64_t* first_roots, uint64_t k,
+                        uint64_t batch, uint8_t* out_xy, int* is_inf);
+
 /* Interpolation through the k consecutive nodes x_i = first_x + i (what every kzg::blob holds, src/blob.cpp:20-48):
  * replaces polyfit (src/util.cpp:180-184, used by poly::from_blob src/poly.cpp:4-6) and linear_roots_and_polyfit
  * (src/util.cpp:172-178, used by verify_proof src/trusted_setup.cpp:239).  ys: k*SB bytes; coeffs_out: the k

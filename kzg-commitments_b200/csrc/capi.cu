@@ -115,6 +115,10 @@ int kzg_gpu_poly_eval_range(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n,
 int kzg_gpu_prove(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out_xy, int* is_inf) {
   return ctx ? ctx->prove(coeffs, n, first_root, k, out_xy, is_inf) : KZG_GPU_ERR_ARG;
 }
+int kzg_gpu_prove_batch(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, const int64_t* first_roots, uint64_t k,
+                        uint64_t batch, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->prove_batch(coeffs, n, first_roots, k, batch, out_xy, is_inf) : KZG_GPU_ERR_ARG;
+}
 int kzg_gpu_interpolate_range(kzg_gpu_ctx* ctx, const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out,
                                uint8_t* vanishing_out) {
   return ctx ? ctx->interpolate(ys, first_x, k, coeffs_out, vanishing_out) : KZG_GPU_ERR_ARG;

@@ -82,6 +82,8 @@ struct kzg_gpu_ctx {
   virtual int poly_quotient(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* q_out) = 0;
   virtual int poly_eval(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* y_out) = 0;
   virtual int prove(const uint8_t* coeffs, uint64_t n, int64_t first_root, uint64_t k, uint8_t* out, int* is_inf) = 0;
+  virtual int prove_batch(const uint8_t* coeffs, uint64_t n, const int64_t* first_roots, uint64_t k, uint64_t batch,
+                          uint8_t* out, int* is_inf) = 0;
   virtual int interpolate(const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out, uint8_t* vanish_out) = 0;
   virtual int microbench(int kind, double* ops) = 0;
   virtual int selftest(int* failures) = 0;
@@ -129,7 +131,7 @@ struct Ctx final : kzg_gpu_ctx {
   // scratch
   DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
       out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3, aff_off, aff_a, aff_b, aff_prefix,
-      aff_totals, inv_fact, it_u, it_pa, it_pb, it_za, it_zb;
+      aff_totals, roots, inv_fact, it_u, it_pa, it_pb, it_za, it_zb;
   uint64_t inv_fact_n = 0;
   // description of the most recent launch, for fetch()
   uint64_t last_batch = 0;
@@ -139,7 +141,7 @@ struct Ctx final : kzg_gpu_ctx {
     cudaSetDevice(device);
     for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
-                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
+                      &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
     for (cudaEvent_t e : phase_ev) if (e) cudaEventDestroy(e);
     if (stream) cudaStreamDestroy(stream);
@@ -553,11 +555,14 @@ struct Ctx final : kzg_gpu_ctx {
     return KZG_GPU_OK;
   }
   // quotient of poly0 by the k consecutive roots -> qbytes (device, (n-k)*SB bytes)
-  int enqueue_quotient(uint64_t n, int64_t first_root, uint64_t k) {
+  // quotients of `batch` polynomials (poly0, stride n) by k consecutive roots each -> qbytes (batch * (n-k) records).
+  // d_roots: device array of the first roots (batched form) or nullptr (single polynomial, first_root).
+  int enqueue_quotient(uint64_t n, int64_t first_root, uint64_t k, uint64_t batch = 1, const long long* d_roots = nullptr) {
     const Fr* q;
     if (k < 48) {  // a few opened points: one CTA-wide suffix scan per root
       constexpr int QT = 512;
-      poly_quotient_rounds<C, QT><<<1, QT, 0, stream>>>(n, (long long)first_root, k, poly0.as<Fr>(), poly1.as<Fr>());
+      poly_quotient_rounds<C, QT><<<(unsigned)batch, QT, 0, stream>>>(n, (long long)first_root, d_roots, k, poly0.as<Fr>(),
+                                                                      poly1.as<Fr>());
       LAUNCHED();
       q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
     } else {       // many: systolic passes of up to ST roots, ping-ponging between the two buffers
@@ -567,7 +572,8 @@ struct Ctx final : kzg_gpu_ctx {
       uint64_t m = n, done = 0;
       while (done < k) {
         const int t = (int)std::min<uint64_t>(ST, k - done);
-        poly_quotient_systolic<C, ST, CHK><<<1, ST, 0, stream>>>(m, (long long)first_root + (long long)done, t, src, dst);
+        poly_quotient_systolic<C, ST, CHK><<<(unsigned)batch, ST, 0, stream>>>(
+            m, n, (long long)first_root + (long long)done, d_roots, (long long)done, t, src, dst);
         LAUNCHED();
         std::swap(src, dst);
         m -= t;
@@ -576,9 +582,9 @@ struct Ctx final : kzg_gpu_ctx {
       q = src;
     }
     const uint64_t nq = n - k;
-    CK(qbytes.ensure(nq * (size_t)SB));
-    unsigned grid = (unsigned)std::min<uint64_t>((nq + 127) / 128, 148 * 8);
-    fr_to_bytes<C><<<grid, 128, 0, stream>>>(nq, q, qbytes.as<uint8_t>());
+    CK(qbytes.ensure(nq * batch * (size_t)SB));
+    unsigned grid = (unsigned)std::min<uint64_t>((nq * batch + 127) / 128, 148 * 8);
+    fr_to_bytes_strided<C><<<grid, 128, 0, stream>>>(nq, batch, n, q, qbytes.as<uint8_t>());
     LAUNCHED();
     return KZG_GPU_OK;
   }
@@ -634,6 +640,35 @@ struct Ctx final : kzg_gpu_ctx {
     if (rc) return rc;
     // same stream: the MSM is ordered after the quotient; qbytes is not touched by the MSM path
     return msm(1, qbytes.as<uint8_t>(), true, n - k, 1, 0, out, is_inf, true);
+  }
+
+  // `batch` proofs in one call: quotients (one CTA per polynomial) feed the batched MSM without leaving the device
+  int prove_batch(const uint8_t* coeffs, uint64_t n, const int64_t* first_roots, uint64_t k, uint64_t batch, uint8_t* out,
+                  int* is_inf) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (srs_n == 0) return KZG_GPU_ERR_STATE;
+    if (!coeffs || !first_roots || k == 0 || batch == 0 || n == 0) return KZG_GPU_ERR_ARG;
+    if (k >= n) {
+      if (out) memset(out, 0, batch * (size_t)(2 * M));
+      if (is_inf) for (uint64_t b = 0; b < batch; b++) is_inf[b] = 1;
+      return KZG_GPU_OK;
+    }
+    if (n - k > srs_n) return KZG_GPU_ERR_ARG;
+    const uint64_t per_pass = std::max<uint64_t>(1, (1ull << 26) / n);  // coefficients per pass
+    for (uint64_t b0 = 0; b0 < batch; b0 += per_pass) {
+      const uint64_t nb = std::min(per_pass, batch - b0);
+      int rc = upload_poly(coeffs + b0 * n * (size_t)SB, n * nb);
+      if (rc) return rc;
+      CK(roots.ensure(nb * sizeof(long long)));
+      CK(cudaMemcpyAsync(roots.p, first_roots + b0, nb * sizeof(long long), cudaMemcpyHostToDevice, stream));
+      rc = enqueue_quotient(n, 0, k, nb, roots.as<long long>());
+      if (rc) return rc;
+      rc = msm(1, qbytes.as<uint8_t>(), true, n - k, nb, 0, out ? out + b0 * (size_t)(2 * M) : nullptr,
+               is_inf ? is_inf + b0 : nullptr, true);
+      if (rc) return rc;
+    }
+    return KZG_GPU_OK;
   }
 
   // interpolation through the consecutive nodes first_x .. first_x + k - 1 (polyfit / linear_roots_and_polyfit)

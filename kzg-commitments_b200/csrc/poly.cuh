@@ -69,20 +69,33 @@ __global__ void fr_to_bytes(uint64_t n, const Field<typename C::FrP>* __restrict
     fr_store<C>(out, i, in[i]);
 }
 
+// batch of polynomials stored with stride `in_stride`: the first nq coefficients of each -> contiguous records
+template <class C>
+__global__ void fr_to_bytes_strided(uint64_t nq, uint64_t batch, uint64_t in_stride, const Field<typename C::FrP>* __restrict__ in,
+                                    uint8_t* __restrict__ out) {
+  const uint64_t total = nq * batch;
+  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t b = t / nq, i = t - b * nq;
+    fr_store<C>(out, t, in[b * in_stride + i]);
+  }
+}
+
 // ---------------------------------------------------------------- quotient by k consecutive linear factors
 // Single CTA.  buf0 holds P (n coefficients, Montgomery); buf1 is scratch of the same size.
 // After round j the current polynomial has n-1-j coefficients.  The result (n-k coefficients) ends
 // in buf0 if k is even, buf1 if k is odd.
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
-poly_quotient_rounds(uint64_t n, long long first_root, uint64_t k, Field<typename C::FrP>* buf0,
-                     Field<typename C::FrP>* buf1) {
+poly_quotient_rounds(uint64_t n, long long first_root, const long long* __restrict__ first_roots, uint64_t k,
+                     Field<typename C::FrP>* buf0, Field<typename C::FrP>* buf1) {
   using Fr = Field<typename C::FrP>;
   __shared__ Fr s_val[THREADS];
   __shared__ Fr s_mul[THREADS];
   const int tid = threadIdx.x;
-  Fr* src = buf0;
-  Fr* dst = buf1;
+  // batched form: CTA b works on polynomial b (stride n) opened at first_roots[b]
+  if (first_roots) first_root = first_roots[blockIdx.x];
+  Fr* src = buf0 + (uint64_t)blockIdx.x * n;
+  Fr* dst = buf1 + (uint64_t)blockIdx.x * n;
   uint64_t m = n;  // current coefficient count
   for (uint64_t round = 0; round < k; round++) {
     const Fr a = fr_from_i64<C>(first_root + (long long)round);
@@ -134,12 +147,16 @@ poly_quotient_rounds(uint64_t n, long long first_root, uint64_t k, Field<typenam
 // One CTA, T stages per pass; the host chains passes for k > T.  dst receives m - t coefficients.
 template <class C, int T, int CHK>
 __global__ void __launch_bounds__(T)
-poly_quotient_systolic(uint64_t m, long long first_root, int t, const Field<typename C::FrP>* __restrict__ src,
+poly_quotient_systolic(uint64_t m, uint64_t stride, long long first_root, const long long* __restrict__ first_roots,
+                       long long root_shift, int t, const Field<typename C::FrP>* __restrict__ src,
                        Field<typename C::FrP>* __restrict__ dst) {
   using Fr = Field<typename C::FrP>;
   __shared__ Fr link[2][T];
   __shared__ Fr feed[CHK];
   const int j = threadIdx.x;
+  if (first_roots) first_root = first_roots[blockIdx.x] + root_shift;  // batched form: CTA b = polynomial b
+  src += (uint64_t)blockIdx.x * stride;
+  dst += (uint64_t)blockIdx.x * stride;
   const Fr a = fr_from_i64<C>(first_root + (long long)j);
   Fr carry = Fr::zero();
   const uint64_t steps = m + (uint64_t)t;

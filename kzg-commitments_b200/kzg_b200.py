@@ -69,6 +69,7 @@ def load_library():
         "kzg_gpu_poly_eval_range": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
         "kzg_gpu_prove": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p, ip]),
         "kzg_gpu_interpolate_range": (ctypes.c_int, [vp, u8p, i64, u64, u8p, u8p]),
+        "kzg_gpu_prove_batch": (ctypes.c_int, [vp, vp, u64, ctypes.POINTER(ctypes.c_int64), u64, u64, u8p, ip]),
         "kzg_gpu_ctx_stream": (vp, [vp]),
         "kzg_gpu_launch_count": (u64, [vp]),
         "kzg_gpu_microbench": (ctypes.c_int, [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
@@ -91,7 +92,7 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_msm_fetch_partial", "kzg_gpu_g1_sum_partials", "kzg_gpu_poly_quotient", "kzg_gpu_poly_eval_range",
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
     "kzg_gpu_phase_times", "kzg_gpu_msm_stats", "kzg_gpu_msm_partial_device", "kzg_gpu_g1_sum_partials_device",
-    "kzg_gpu_interpolate_range",
+    "kzg_gpu_interpolate_range", "kzg_gpu_prove_batch",
 ]
 
 
@@ -246,6 +247,14 @@ class Context:
         inf = ctypes.c_int(0)
         self._check(self.lib.kzg_gpu_prove(self.h, coeffs, n, first_root, k, out, ctypes.byref(inf)), "prove")
         return out.raw, bool(inf.value)
+
+    def prove_batch(self, coeffs, n, first_roots, k):
+        batch = len(first_roots)
+        out = ctypes.create_string_buffer(batch * 2 * self.M)
+        inf = (ctypes.c_int * batch)()
+        roots = (ctypes.c_int64 * batch)(*first_roots)
+        self._check(self.lib.kzg_gpu_prove_batch(self.h, _ptr(coeffs), n, roots, k, batch, out, inf), "prove_batch")
+        return out.raw, [bool(v) for v in inf]
 
     @property
     def stream(self):

@@ -27,6 +27,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "gpu_side.h"
@@ -83,11 +84,23 @@ ECP2 g2_from_body(const uint8_t* xy, int is_inf) {
 }
 
 // coefficients of P as flat little-endian CURVE_ORDER_BYTES records (what BIG_from_ZZ starts from, util.cpp:31-43)
+// BytesFromZZ only reads the coefficient's magnitude (no ZZ_p modulus context involved), so large polynomials are
+// packed by a few host threads: at 0.2-0.4 us per coefficient the single-threaded loop (1.2 ms for 4097
+// coefficients) would otherwise cost more than the 1.0 ms device MSM it feeds (SURVEY.md §7.4 "host marshalling").
 std::vector<uint8_t> pack_coeffs(const ZZ_pX& P) {
   const long n = deg(P) + 1;
   const int SB = kzg::CURVE_ORDER_BYTES;
   std::vector<uint8_t> raw((size_t)n * SB);
-  for (long i = 0; i < n; i++) BytesFromZZ(raw.data() + (size_t)i * SB, rep(P[i]), SB);
+  auto pack = [&](long lo, long hi) {
+    for (long i = lo; i < hi; i++) BytesFromZZ(raw.data() + (size_t)i * SB, rep(P[i]), SB);
+  };
+  unsigned hw = std::thread::hardware_concurrency();
+  const long nt = n < 2048 ? 1 : (long)std::min<unsigned>(hw ? hw : 4, 8);
+  if (nt == 1) { pack(0, n); return raw; }
+  std::vector<std::thread> pool;
+  for (long t = 1; t < nt; t++) pool.emplace_back(pack, n * t / nt, n * (t + 1) / nt);
+  pack(0, n / nt);
+  for (auto& th : pool) th.join();
   return raw;
 }
 

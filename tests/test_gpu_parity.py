@@ -395,3 +395,25 @@ def test_interpolation_matches_reference_and_round_trips(ctxs, cname):
         assert Z[-ctx.SB:] == (1).to_bytes(ctx.SB, "little")
     P = kzg_b200.Poly.from_blob(ctx, [ord(ch) for ch in "hello there my name is bob"])
     assert P.coeffs == C.poly_trim(C.interpolate(list(range(26)), [ord(ch) for ch in "hello there my name is bob"]))
+
+
+@pytest.mark.parametrize("cname", ["bls12381", "bn254"])
+def test_prove_batch_equals_single_proofs(ctxs, cname):
+    """kzg_gpu_prove_batch (one CTA per quotient, batched MSM) against kzg_gpu_prove, scan and systolic paths."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(55 + C.id)
+    n, batch = 700, 5
+    ts = kzg_b200.TrustedSetup.generate(cname, n + 1, rng.randrange(C.r), ctx=ctx)
+    polys = [[rng.randrange(C.r) for _ in range(n)] for _ in range(batch)]
+    polys[3] = [0] * n
+    raw = b"".join(C.scalars_to_bytes(p) for p in polys)
+    for k in (1, 3, 64):
+        roots = [rng.randrange(0, 50) for _ in range(batch)]
+        out, infs = ctx.prove_batch(raw, n, roots, k)
+        for b in range(batch):
+            xy, inf = ctx.prove(C.scalars_to_bytes(polys[b]), roots[b], k)
+            assert out[b * 2 * ctx.M:(b + 1) * 2 * ctx.M] == xy and infs[b] == inf, (k, b)
+        assert infs[3]
+    out, infs = ctx.prove_batch(raw, n, [0] * batch, n)
+    assert all(infs) and out == bytes(len(out))
