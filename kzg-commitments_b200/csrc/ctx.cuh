@@ -20,6 +20,7 @@
 #include "diag.cuh"
 #include "msm.cuh"
 #include "msm_affine.cuh"
+#include "msm_team.cuh"
 #include "poly.cuh"
 #include "setup.cuh"
 
@@ -66,7 +67,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -239,8 +240,13 @@ struct Ctx final : kzg_gpu_ctx {
       PairJob<F> j0{in0, out0, len0 > 1 ? sums0 * (len0 / 2) : 0};
       PairJob<F> j1{in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0};
       const uint64_t mx = std::max(j0.n_out, j1.n_out);
-      dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)148 * 64), 2);
-      msm_pair_sum<F><<<grid, 128, 0, stream>>>(j0, j1);
+      if (opt_team && j0.n_out + j1.n_out <= TEAM_MAX_ITEMS) {  // latency-bound level: 4 lanes per addition
+        dim3 grid((unsigned)((4 * mx + 127) / 128), 2);
+        msm_pair_sum_team<F><<<grid, 128, 0, stream>>>(j0, j1);
+      } else {
+        dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)148 * 64), 2);
+        msm_pair_sum<F><<<grid, 128, 0, stream>>>(j0, j1);
+      }
       LAUNCHED();
       if (len0 > 1) { std::swap(in0, out0); len0 /= 2; }
       if (len1 > 1) { std::swap(in1, out1); len1 /= 2; }
@@ -382,9 +388,14 @@ struct Ctx final : kzg_gpu_ctx {
       int fold_levels = 0;
       while ((1ull << fold_levels) < max_tasks && fold_levels < 31) fold_levels++;  // bound on ceil(log2(max tasks in a bucket))
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 32);
+      unsigned grid_team = (unsigned)std::min<uint64_t>((4 * max_tasks + 127) / 128, (uint64_t)sms * 128);
       for (int l = 0; l < fold_levels; l++) {
-        msm_fold_level<F><<<grid, 128, 0, stream>>>(l, task_first.as<uint32_t>() + nbuckets, d_hist + MSM_MAX_CHUNK + 1,
-                                                    slot_seg.as<MsmSlotSeg>(), partial.as<XYZZ<F>>());
+        if (opt_team)  // the pairs of one level are few (buckets with several tasks): latency-bound
+          msm_fold_level_team<F><<<grid_team, 128, 0, stream>>>(l, task_first.as<uint32_t>() + nbuckets, d_hist + MSM_MAX_CHUNK + 1,
+                                                                slot_seg.as<MsmSlotSeg>(), partial.as<XYZZ<F>>());
+        else
+          msm_fold_level<F><<<grid, 128, 0, stream>>>(l, task_first.as<uint32_t>() + nbuckets, d_hist + MSM_MAX_CHUNK + 1,
+                                                      slot_seg.as<MsmSlotSeg>(), partial.as<XYZZ<F>>());
         LAUNCHED();
       }
     }
@@ -394,8 +405,13 @@ struct Ctx final : kzg_gpu_ctx {
       BucketJob<F> jr{rin, R, Cn, Cn, 1, groups * R * Lr};
       BucketJob<F> jc{cin, Cn, R, 1, Cn, groups * Cn * Lc};
       const uint64_t mx = std::max(jr.total, jc.total);
-      dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)sms * 64), 2);
-      msm_bucket_pairs<F><<<grid, 128, 0, stream>>>((uint64_t)sh.nb, task_first.as<uint32_t>(), partial.as<XYZZ<F>>(), jr, jc);
+      if (opt_team && jr.total + jc.total <= TEAM_MAX_ITEMS) {
+        dim3 grid((unsigned)((4 * mx + 127) / 128), 2);
+        msm_bucket_pairs_team<F><<<grid, 128, 0, stream>>>((uint64_t)sh.nb, task_first.as<uint32_t>(), partial.as<XYZZ<F>>(), jr, jc);
+      } else {
+        dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)sms * 64), 2);
+        msm_bucket_pairs<F><<<grid, 128, 0, stream>>>((uint64_t)sh.nb, task_first.as<uint32_t>(), partial.as<XYZZ<F>>(), jr, jc);
+      }
       LAUNCHED();
       rc = enqueue_pair_trees<F>(rin, rout, groups * R, Lr, cin, cout, groups * Cn, Lc);
       if (rc) return rc;
@@ -404,8 +420,13 @@ struct Ctx final : kzg_gpu_ctx {
       WeightedJob<F> wr{rin, rout, R, groups * Pr, 0u};
       WeightedJob<F> wc{cin, cout, Cn, groups * Pc, 1u};
       const uint64_t mw = std::max(wr.total, wc.total);
-      dim3 gridw((unsigned)std::min<uint64_t>((mw + 127) / 128, (uint64_t)sms * 64), 2);
-      msm_weighted_chunks<F><<<gridw, 128, 0, stream>>>(wr, wc);
+      if (opt_team && wr.total + wc.total <= TEAM_MAX_ITEMS) {
+        dim3 gridw((unsigned)((4 * mw + 127) / 128), 2);
+        msm_weighted_chunks_team<F><<<gridw, 128, 0, stream>>>(wr, wc);
+      } else {
+        dim3 gridw((unsigned)std::min<uint64_t>((mw + 127) / 128, (uint64_t)sms * 64), 2);
+        msm_weighted_chunks<F><<<gridw, 128, 0, stream>>>(wr, wc);
+      }
       LAUNCHED();
       std::swap(rin, rout);
       std::swap(cin, cout);
@@ -413,7 +434,10 @@ struct Ctx final : kzg_gpu_ctx {
       if (rc) return rc;
     }
     const XYZZ<F>*t1 = rin, *t2 = cin;
-    msm_group_combine<F><<<(unsigned)((groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
+    if (opt_team && groups <= TEAM_MAX_ITEMS)
+      msm_group_combine_team<F><<<(unsigned)((4 * groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
+    else
+      msm_group_combine<F><<<(unsigned)((groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
     LAUNCHED();
     phase_mark(3);
     msm_finish<F><<<(unsigned)((batch + 31) / 32), 32, 0, stream>>>(

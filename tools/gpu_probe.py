@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--chunks", default="0")
     ap.add_argument("--precompute", default="0")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--team", default="1")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     ctx = kzg_b200.Context(args.curve, 0)
@@ -51,8 +52,9 @@ def main():
                 t0 = time.time()
                 ctx.setup_powers(12345678901234567890123, n, want_bytes=False)
                 t_setup = time.time() - t0
-                for ch in [int(x) for x in args.chunks.split(",")]:
+                for ch, team in [(int(x), int(y)) for x in args.chunks.split(",") for y in args.team.split(",")]:
                     ctx.set_option("task_chunk", ch)
+                    ctx.set_option("team", team)
                     times = []
                     for rep in range(args.reps + 1):
                         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -62,7 +64,7 @@ def main():
                         e1.synchronize()
                         times.append(e0.elapsed_time(e1))
                     xy, inf = ctx.msm_fetch(1)
-                    row = {"log2n": lg, "precompute": pre, "window_bits": wb, "task_chunk": ch, "ms": min(times[1:]),
+                    row = {"log2n": lg, "precompute": pre, "window_bits": wb, "task_chunk": ch, "team": team, "ms": min(times[1:]),
                            "first_ms": times[0], "mpts_per_s": n / min(times[1:]) / 1e3, "setup_s": t_setup,
                            "xy": xy[:8].hex(), "phases": ctx.phase_times(), "stats": ctx.msm_stats()}
                     res["msm"].append(row)
