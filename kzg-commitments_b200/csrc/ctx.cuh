@@ -385,12 +385,16 @@ struct Ctx final : kzg_gpu_ctx {
     }
     phase_mark(2);
     {
+      // a bucket of one window holds at most `count` records, i.e. at most ceil(count / chunk) + 1 tasks; levels
+      // beyond the largest task count actually present (max_nt, on the device) return at once, so their grid is
+      // kept small: the pairs of a level are few and found by a grid-stride scan of slot_seg
+      const uint64_t nt_bound = std::min<uint64_t>(max_tasks, count / (uint64_t)sh.chunk + 2);
       int fold_levels = 0;
-      while ((1ull << fold_levels) < max_tasks && fold_levels < 31) fold_levels++;  // bound on ceil(log2(max tasks in a bucket))
-      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 32);
-      unsigned grid_team = (unsigned)std::min<uint64_t>((4 * max_tasks + 127) / 128, (uint64_t)sms * 128);
+      while ((1ull << fold_levels) < nt_bound && fold_levels < 31) fold_levels++;
+      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 8);
+      unsigned grid_team = (unsigned)std::min<uint64_t>((4 * max_tasks + 127) / 128, (uint64_t)sms * 8);
       for (int l = 0; l < fold_levels; l++) {
-        if (opt_team)  // the pairs of one level are few (buckets with several tasks): latency-bound
+        if (opt_team)
           msm_fold_level_team<F><<<grid_team, 128, 0, stream>>>(l, task_first.as<uint32_t>() + nbuckets, d_hist + MSM_MAX_CHUNK + 1,
                                                                 slot_seg.as<MsmSlotSeg>(), partial.as<XYZZ<F>>());
         else

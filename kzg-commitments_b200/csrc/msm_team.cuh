@@ -6,7 +6,7 @@
 // lanes share one group operation: the independent products of each formula step run on different
 // lanes and the operands travel by warp shuffles, so an addition is 5 product rounds deep instead of
 // 14 and a doubling 3 instead of 9.  It spends ~40 % more multiplier work per operation, so the host
-// (ctx.cuh) picks these kernels only for levels of at most TEAM_MAX_ITEMS items; wide levels keep
+// (ctx.cuh) picks these kernels only for levels of at most TEAM_MAX_ITEMS items (measured cross-over on B200); wide levels keep
 // the one-thread-per-item kernels of msm.cuh.  Point values are replicated on the four lanes, which
 // keeps every branch uniform inside a team; shuffles name only the team's own lanes in their mask.
 #pragma once
@@ -15,7 +15,7 @@
 #if defined(__CUDACC__)
 namespace kzgb200 {
 
-constexpr uint64_t TEAM_MAX_ITEMS = 16384;
+constexpr uint64_t TEAM_MAX_ITEMS = 200000;
 
 template <class P>
 __device__ __forceinline__ Field<P> team_shfl(unsigned mask, const Field<P>& v, int src) {
@@ -157,7 +157,7 @@ msm_bucket_pairs_team(uint64_t nb, const uint32_t* __restrict__ task_first, cons
 }
 
 template <class F>
-__global__ void __launch_bounds__(128) msm_pair_sum_team(PairJob<F> j0, PairJob<F> j1) {
+__global__ void __launch_bounds__(128, 4) msm_pair_sum_team(PairJob<F> j0, PairJob<F> j1) {
   const PairJob<F>& jb = blockIdx.y ? j1 : j0;
   KZG_TEAM_LOOP(i, jb.n_out) {
     const XYZZ<F> a = jb.in[2 * i], b = jb.in[2 * i + 1];
