@@ -385,10 +385,11 @@ struct Ctx final : kzg_gpu_ctx {
     }
     phase_mark(2);
     {
-      // a bucket of one window holds at most `count` records, i.e. at most ceil(count / chunk) + 1 tasks; levels
+      // a bucket holds at most `count` records (count * W with the window table, where all windows share one
+      // bucket space), i.e. at most ceil(that / chunk) + 1 tasks; levels
       // beyond the largest task count actually present (max_nt, on the device) return at once, so their grid is
       // kept small: the pairs of a level are few and found by a grid-stride scan of slot_seg
-      const uint64_t nt_bound = std::min<uint64_t>(max_tasks, count / (uint64_t)sh.chunk + 2);
+      const uint64_t nt_bound = std::min<uint64_t>(max_tasks, count * (uint64_t)(precomp ? sh.W : 1) / (uint64_t)sh.chunk + 2);
       int fold_levels = 0;
       while ((1ull << fold_levels) < nt_bound && fold_levels < 31) fold_levels++;
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 8);

@@ -17,7 +17,7 @@
 namespace kzgb200 {
 
 template <class P>
-struct Field {
+struct alignas((P::L % 4 == 0) ? 16 : 8) Field {  // aligned for 128-bit (64-bit for 6 limbs) loads and stores
   static constexpr int L = P::L;
   using Params = P;
   uint32_t v[L];
