@@ -15,7 +15,7 @@
 #if defined(__CUDACC__)
 namespace kzgb200 {
 
-constexpr uint64_t TEAM_MAX_ITEMS = 200000;
+constexpr uint64_t TEAM_MAX_ITEMS = 100000;
 
 template <class P>
 __device__ __forceinline__ Field<P> team_shfl(unsigned mask, const Field<P>& v, int src) {

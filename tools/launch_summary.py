@@ -1,0 +1,17 @@
+"""Summarise an ncu launch list (--metrics gpu__time_duration.sum --csv): per-kernel totals of the LAST MSM pass in the file.
+    python tools/launch_summary.py gpurun_out/launches.csv [--detail]"""
+import csv, re, sys
+from collections import OrderedDict
+rows = [l for l in open(sys.argv[1]) if l.startswith('"')]
+r = list(csv.reader(rows))
+hdr = r[0]; ki = hdr.index('Kernel Name'); vi = hdr.index('Metric Value'); ui = hdr.index('Metric Unit')
+ks = [(re.sub(r'^void ', '', re.sub(r'[<(].*', '', x[ki])), float(x[vi].replace(',', '')) / (1000 if x[ui] == 'ns' else 1)) for x in r[1:]]
+last = [i for i, k in enumerate(ks) if k[0] == 'msm_digits'][-1]
+agg = OrderedDict(); tot = 0
+for n, v in ks[last:]:
+    a = agg.setdefault(n, [0, 0]); a[0] += v; a[1] += 1; tot += v
+for n, (v, c) in agg.items():
+    print(f"{n:28s} x{c:<3d} {v:9.1f} us  {100 * v / tot:5.1f} %")
+print(f"{'total':28s}      {tot:9.1f} us")
+if '--detail' in sys.argv:
+    print('; '.join(f"{n} {v:.1f}" for n, v in ks[last:] if n.startswith(('msm_pair', 'msm_weighted', 'msm_group', 'msm_fold', 'msm_bucket'))))
