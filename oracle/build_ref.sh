@@ -6,6 +6,7 @@
 #   oracle/_ref/kzgref-$c        our harness (oracle/ref_harness.cpp) linked against the reference
 #   oracle/_ref/benchmark-$c     the reference's own benchmark/benchmark.cpp, unmodified
 #   oracle/_ref/testing-bn254    the reference's own testing/testing.cpp, unmodified
+#   oracle/_ref/kzg-cli-bn254    the reference's demo CLI demo/shared/kzg-cli.cpp, unmodified
 # Nothing from /root/reference is copied into tracked paths; the scratch copy lives in
 # oracle/_ref/scratch (listed in .gpurunignore).
 #
@@ -49,6 +50,7 @@ build_curve() {  # $1=lower name  $2=MIRACL curve tag  $3=BIG tag
   g++ -O2 $I "$REF/benchmark/benchmark.cpp" $L -o "$OUT/benchmark-$c"
   if [ "$c" = bn254 ]; then
     g++ -O2 $I "$REF/testing/testing.cpp" $L -o "$OUT/testing-bn254"
+    g++ -O2 $I "$REF/demo/shared/kzg-cli.cpp" $L -o "$OUT/kzg-cli-bn254"   # the demo CLI (reference Makefile:14-15)
   fi
 }
 build_curve bls12381 BLS12381 B384_58 &

@@ -5,6 +5,7 @@
 # kzg-commitments_b200/libkzg_gpu.so.  Then links the reference's own callers against it, unchanged:
 #   oracle/_ref/dropin/testing-bn254-gpu        testing/testing.cpp   (36 property checks)
 #   oracle/_ref/dropin/benchmark-<curve>-gpu    benchmark/benchmark.cpp
+#   oracle/_ref/dropin/kzg-cli-bn254-gpu        demo/shared/kzg-cli.cpp (the demo's setup / commit / prove / verify CLI)
 #   oracle/_ref/dropin/kzgdrop-<curve>          oracle/ref_harness.cpp (same byte-file driver as kzgref-<curve>)
 # Needs oracle/build_ref.sh to have run (MIRACL core.a, NTL ntl.a and generated headers in oracle/_ref/scratch).
 # Outputs are git-ignored and travel to the GPU box like the other built artefacts; /root/reference is
@@ -37,6 +38,7 @@ build_curve() {
   g++ -O2 $I "$REF/benchmark/benchmark.cpp" $L -o "$OUT/benchmark-$c-gpu"
   if [ "$c" = bn254 ]; then
     g++ -O2 $I "$REF/testing/testing.cpp" $L -o "$OUT/testing-bn254-gpu"
+    g++ -O2 $I "$REF/demo/shared/kzg-cli.cpp" $L -o "$OUT/kzg-cli-bn254-gpu"
     cp "$REF/testing/blob1.txt" "$REF/testing/blob2.txt" "$OUT/" 2>/dev/null || true
   fi
 }

@@ -103,3 +103,41 @@ def test_dropin_trusted_setup_is_loadable_by_reference():
         _run(drop, "prove", f("srs"), f("c"), 2, 5, f("p1"))
         _run(ref, "prove", f("srs"), f("c"), 2, 5, f("p2"))
         assert open(f("p1"), "rb").read() == open(f("p2"), "rb").read()
+
+
+def test_demo_cli_flow_cross_process():
+    """the reference's demo CLI (demo/shared/kzg-cli.cpp, unmodified) linked against the drop-in,
+    driven the way demo/run-demo drives it — setup 65536, commit a 142 KB document (4583 chunks of 31 bytes),
+    random 4-chunk subsection proofs, verify — with the UNMODIFIED reference CLI as the other party: it loads
+    the GPU-made kzg_public file, must produce the same commitment and proof hex, and must accept / reject
+    the same transcripts."""
+    import random
+    gpu = _need(os.path.join(DROPIN, "kzg-cli-bn254-gpu"))
+    ref = _need(os.path.join(REF, "kzg-cli-bn254"))
+    rng = random.Random(142054)
+    words = ["kzg", "commit", "proof", "ledger", "peer", "host", "block", "chunk", "pairing", "setup", "\n", "blob"]
+    doc = ""
+    while len(doc) < 142054:
+        doc += rng.choice(words) + " "
+    doc = doc[:142054]
+    with tempfile.TemporaryDirectory() as td:
+        shared, peer = os.path.join(td, "shared"), os.path.join(td, "peer-a")
+        os.mkdir(shared)
+        os.mkdir(peer)
+        with open(os.path.join(peer, "document.txt"), "w") as f:
+            f.write(doc)
+        out = _run(gpu, "setup", 65536, cwd=shared)
+        assert "num_coeff=65536" in out and os.path.getsize(os.path.join(shared, "kzg_public")) > 65536 * 3 * 32
+        commit = _run(gpu, "commit", "document.txt", cwd=peer).strip()
+        assert re.fullmatch(r"[0-9a-f]+", commit)
+        assert _run(ref, "commit", "document.txt", cwd=peer, timeout=1200).strip() == commit
+        for seed in (7, 123456789):
+            proof, offset, data = _run(gpu, "prove", "document.txt", seed, cwd=peer).split()
+            if seed == 7:  # the reference prover takes seconds per proof: compare one
+                assert _run(ref, "prove", "document.txt", seed, cwd=peer, timeout=1200).split() == [proof, offset, data]
+            for cli in (gpu, ref):
+                ok = subprocess.run([cli, "verify", commit, proof, offset, data], cwd=peer, capture_output=True, timeout=1200)
+                assert ok.returncode == 0, (cli, ok.stderr)
+                bad = data[:10] + ("0" if data[10] != "0" else "1") + data[11:]
+                no = subprocess.run([cli, "verify", commit, proof, offset, bad], cwd=peer, capture_output=True, timeout=1200)
+                assert no.returncode == 1, (cli, no.stderr)
