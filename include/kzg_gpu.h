@@ -14,6 +14,7 @@
  *   kzg_gpu_poly_eval_range        evaluate_polynomial_points     src/util.cpp:186-211
  *   kzg_gpu_prove                  create_proof body              src/trusted_setup.cpp:214-228
  *   kzg_gpu_interpolate_range      polyfit / linear_roots_and_polyfit   src/util.cpp:172-184 (consecutive nodes)
+ *   kzg_gpu_commit_bytes           blob::from_bytes + poly::from_blob + create_commit   src/blob.cpp:19-48
  *   kzg_gpu_setup_powers           trusted_setup(int) + generate_elements_range
  *                                                                 src/trusted_setup.cpp:21-74, 123-135
  *   kzg_gpu_srs_load               the _G1/_G2 vectors a trusted_setup holds (src/kzg.h:183-185),
@@ -128,6 +129,14 @@ int kzg_gpu_prove_batch(kzg_gpu_ctx* ctx, const uint8_t* coeffs, uint64_t n, con
  * Z = prod (x - x_i) or NULL. */
 int kzg_gpu_interpolate_range(kzg_gpu_ctx* ctx, const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out,
                               uint8_t* vanishing_out);
+
+/* Document bytes to commitment without leaving the device: blob::from_bytes (src/blob.cpp:19-48: chunk i of chunk_size
+ * bytes, zero-padded, little-endian, at node chunk_offset + i) -> poly::from_blob (src/poly.cpp:4-6) -> create_commit
+ * (src/trusted_setup.cpp:137-147).  chunk_size in 1..SB-1 (MAX_CHUNK_BYTES, src/kzg.h:31) and byte_length a multiple of
+ * it, else KZG_GPU_ERR_ARG (the reference throws invalid_argument); byte_length / chunk_size <= SRS size.
+ * coeffs_out: NULL or byte_length/chunk_size * SB bytes receiving the polynomial (for later create_proof calls). */
+int kzg_gpu_commit_bytes(kzg_gpu_ctx* ctx, const uint8_t* bytes, uint64_t byte_length, int chunk_size, int64_t chunk_offset,
+                         uint8_t* coeffs_out, uint8_t* out_xy /* 2M */, int* is_inf);
 
 /* The context's CUDA stream (cudaStream_t) so a caller can time with events on it. */
 void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx);

@@ -124,6 +124,10 @@ int kzg_gpu_interpolate_range(kzg_gpu_ctx* ctx, const uint8_t* ys, int64_t first
                                uint8_t* vanishing_out) {
   return ctx ? ctx->interpolate(ys, first_x, k, coeffs_out, vanishing_out) : KZG_GPU_ERR_ARG;
 }
+int kzg_gpu_commit_bytes(kzg_gpu_ctx* ctx, const uint8_t* bytes, uint64_t byte_length, int chunk_size, int64_t chunk_offset,
+                         uint8_t* coeffs_out, uint8_t* out_xy, int* is_inf) {
+  return ctx ? ctx->commit_bytes(bytes, byte_length, chunk_size, chunk_offset, coeffs_out, out_xy, is_inf) : KZG_GPU_ERR_ARG;
+}
 void* kzg_gpu_ctx_stream(kzg_gpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 uint64_t kzg_gpu_launch_count(const kzg_gpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
 int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops) { return ctx ? ctx->microbench(kind, ops) : KZG_GPU_ERR_ARG; }

@@ -86,6 +86,8 @@ struct kzg_gpu_ctx {
   virtual int prove_batch(const uint8_t* coeffs, uint64_t n, const int64_t* first_roots, uint64_t k, uint64_t batch,
                           uint8_t* out, int* is_inf) = 0;
   virtual int interpolate(const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out, uint8_t* vanish_out) = 0;
+  virtual int commit_bytes(const uint8_t* bytes, uint64_t byte_length, int chunk_size, int64_t chunk_offset,
+                           uint8_t* coeffs_out, uint8_t* out, int* is_inf) = 0;
   virtual int microbench(int kind, double* ops) = 0;
   virtual int selftest(int* failures) = 0;
   virtual int phase_times(float* ms, int n) = 0;
@@ -130,7 +132,7 @@ struct Ctx final : kzg_gpu_ctx {
   DevBuf fb1, fb2;
   bool fb_ready = false;
   // scratch
-  DevBuf stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
+  DevBuf raw, stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
       out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3, aff_off, aff_a, aff_b, aff_prefix,
       aff_totals, roots, inv_fact, it_u, it_pa, it_pb, it_za, it_zb;
   uint64_t inv_fact_n = 0;
@@ -140,7 +142,7 @@ struct Ctx final : kzg_gpu_ctx {
 
   ~Ctx() override {
     cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &stage, &scal, &digits, &counts, &starts, &task_first,
+    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &raw, &stage, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
                       &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
@@ -700,11 +702,9 @@ struct Ctx final : kzg_gpu_ctx {
     return KZG_GPU_OK;
   }
 
-  // interpolation through the consecutive nodes first_x .. first_x + k - 1 (polyfit / linear_roots_and_polyfit)
-  int interpolate(const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out, uint8_t* vanish_out) override {
-    std::lock_guard<std::recursive_mutex> lock(mu);
-    CK(cudaSetDevice(device));
-    if (!ys || k == 0 || k > (1ull << 22) || (!coeffs_out && !vanish_out)) return KZG_GPU_ERR_ARG;
+  // interpolation through the consecutive nodes first_x .. first_x + k - 1 of the k values in `stage` (device, SB-byte
+  // little-endian each); leaves the interpolant in *p_out (k coefficients) and the vanishing polynomial in *z_out (k + 1)
+  int enqueue_interpolate(int64_t first_x, uint64_t k, Fr** p_out, Fr** z_out) {
     uint64_t kp = 1;
     while (kp < k) kp <<= 1;
     if (inv_fact_n < k) {  // 1/t! table, cached
@@ -714,14 +714,12 @@ struct Ctx final : kzg_gpu_ctx {
       LAUNCHED();
       inv_fact_n = want;
     }
-    CK(stage.ensure(k * (size_t)SB));
     CK(it_u.ensure(k * sizeof(Fr)));
     CK(it_pa.ensure(kp * sizeof(Fr)));
     CK(it_pb.ensure(kp * sizeof(Fr)));
     CK(it_za.ensure(2 * kp * sizeof(Fr)));
     CK(it_zb.ensure(2 * kp * sizeof(Fr)));
     CK(qbytes.ensure((kp + 1) * (size_t)SB));
-    CK(cudaMemcpyAsync(stage.p, ys, k * (size_t)SB, cudaMemcpyHostToDevice, stream));
     interp_scale_values<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(
         k, stage.as<uint8_t>(), inv_fact.as<Fr>(), it_u.as<Fr>());
     LAUNCHED();
@@ -736,6 +734,21 @@ struct Ctx final : kzg_gpu_ctx {
       std::swap(pin, pout);
       std::swap(zin, zout);
     }
+    *p_out = pin;
+    *z_out = zin;
+    return KZG_GPU_OK;
+  }
+
+  // polyfit / linear_roots_and_polyfit for a blob's consecutive nodes
+  int interpolate(const uint8_t* ys, int64_t first_x, uint64_t k, uint8_t* coeffs_out, uint8_t* vanish_out) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (!ys || k == 0 || k > (1ull << 22) || (!coeffs_out && !vanish_out)) return KZG_GPU_ERR_ARG;
+    CK(stage.ensure(k * (size_t)SB));
+    CK(cudaMemcpyAsync(stage.p, ys, k * (size_t)SB, cudaMemcpyHostToDevice, stream));
+    Fr *pin = nullptr, *zin = nullptr;
+    int rc = enqueue_interpolate(first_x, k, &pin, &zin);
+    if (rc) return rc;
     if (coeffs_out) {
       fr_to_bytes<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(k, pin, qbytes.as<uint8_t>());
       LAUNCHED();
@@ -749,6 +762,36 @@ struct Ctx final : kzg_gpu_ctx {
       CK(cudaStreamSynchronize(stream));
     }
     return KZG_GPU_OK;
+  }
+
+  // blob::from_bytes -> poly::from_blob -> create_commit chained on the device: raw bytes in, commitment out
+  // (src/blob.cpp:19-48, src/poly.cpp:4-6, src/trusted_setup.cpp:137-147); only the document crosses the bus.
+  int commit_bytes(const uint8_t* bytes, uint64_t byte_length, int chunk_size, int64_t chunk_offset, uint8_t* coeffs_out,
+                   uint8_t* out, int* is_inf) override {
+    std::lock_guard<std::recursive_mutex> lock(mu);
+    CK(cudaSetDevice(device));
+    if (srs_n == 0) return KZG_GPU_ERR_STATE;
+    if (chunk_size < 1 || chunk_size > SB - 1 || byte_length % (uint64_t)chunk_size != 0) return KZG_GPU_ERR_ARG;
+    const uint64_t k = byte_length / (uint64_t)chunk_size;
+    if (k == 0) {
+      if (out) memset(out, 0, 2 * M);
+      if (is_inf) *is_inf = 1;
+      return KZG_GPU_OK;
+    }
+    if (!bytes || k > srs_n || k > (1ull << 22)) return KZG_GPU_ERR_ARG;
+    CK(raw.ensure(byte_length));
+    CK(stage.ensure(k * (size_t)SB));
+    CK(cudaMemcpyAsync(raw.p, bytes, byte_length, cudaMemcpyHostToDevice, stream));
+    blob_encode_chunks<<<(unsigned)std::min<uint64_t>((k * SB + 255) / 256, 148 * 16), 256, 0, stream>>>(
+        k, chunk_size, SB, raw.as<uint8_t>(), stage.as<uint8_t>());
+    LAUNCHED();
+    Fr *pin = nullptr, *zin = nullptr;
+    int rc = enqueue_interpolate(chunk_offset, k, &pin, &zin);
+    if (rc) return rc;
+    fr_to_bytes<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(k, pin, qbytes.as<uint8_t>());
+    LAUNCHED();
+    if (coeffs_out) CK(cudaMemcpyAsync(coeffs_out, qbytes.p, k * (size_t)SB, cudaMemcpyDeviceToHost, stream));
+    return msm(1, qbytes.as<uint8_t>(), true, k, 1, 0, out, is_inf, true);
   }
 
   // ------------------------------------------------------------------ trusted setup

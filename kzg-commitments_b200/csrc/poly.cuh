@@ -253,6 +253,19 @@ __device__ __forceinline__ Fr warp_sum_field(Fr v) {
   return v;  // lane 0 holds the sum
 }
 
+// blob::from_bytes (src/blob.cpp:19-48) on the device: chunk i of chunk_size bytes, zero-padded, read as a
+// little-endian integer (ZZFromBytes) becomes the SB-byte scalar y_i.  chunk_size <= SB - 1 = MAX_CHUNK_BYTES
+// (src/kzg.h:31), so the value is below the group order and conv<ZZ_p> is the identity.
+static __global__ void blob_encode_chunks(uint64_t n_chunks, int chunk_size, int sb, const uint8_t* __restrict__ bytes,
+                                          uint8_t* __restrict__ ys) {
+  const uint64_t total = n_chunks * (uint64_t)sb;
+  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t i = t / (uint64_t)sb;
+    const int j = (int)(t % (uint64_t)sb);
+    ys[t] = j < chunk_size ? bytes[i * (uint64_t)chunk_size + j] : (uint8_t)0;
+  }
+}
+
 // u_i = y_i / i!  (y from little-endian bytes)
 template <class C>
 __global__ void interp_scale_values(uint64_t k, const uint8_t* __restrict__ ys, const Field<typename C::FrP>* __restrict__ inv_fact,

@@ -69,6 +69,7 @@ def load_library():
         "kzg_gpu_poly_eval_range": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
         "kzg_gpu_prove": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p, ip]),
         "kzg_gpu_interpolate_range": (ctypes.c_int, [vp, u8p, i64, u64, u8p, u8p]),
+        "kzg_gpu_commit_bytes": (ctypes.c_int, [vp, vp, u64, ctypes.c_int, i64, u8p, u8p, ctypes.POINTER(ctypes.c_int)]),
         "kzg_gpu_prove_batch": (ctypes.c_int, [vp, vp, u64, ctypes.POINTER(ctypes.c_int64), u64, u64, u8p, ip]),
         "kzg_gpu_ctx_stream": (vp, [vp]),
         "kzg_gpu_launch_count": (u64, [vp]),
@@ -92,7 +93,7 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_msm_fetch_partial", "kzg_gpu_g1_sum_partials", "kzg_gpu_poly_quotient", "kzg_gpu_poly_eval_range",
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
     "kzg_gpu_phase_times", "kzg_gpu_msm_stats", "kzg_gpu_msm_partial_device", "kzg_gpu_g1_sum_partials_device",
-    "kzg_gpu_interpolate_range", "kzg_gpu_prove_batch",
+    "kzg_gpu_interpolate_range", "kzg_gpu_prove_batch", "kzg_gpu_commit_bytes",
 ]
 
 
@@ -240,6 +241,16 @@ class Context:
         van = ctypes.create_string_buffer((k + 1) * self.SB) if want_vanishing else None
         self._check(self.lib.kzg_gpu_interpolate_range(self.h, ys, first_x, k, out, van), "interpolate_range")
         return out.raw, (van.raw if want_vanishing else None)
+
+    def commit_bytes(self, data, chunk_size, chunk_offset=0, want_coeffs=True):
+        """blob::from_bytes + poly::from_blob + create_commit on the device: (xy, is_inf, coefficient bytes or None)."""
+        k = len(data) // chunk_size if chunk_size > 0 else 0
+        out = ctypes.create_string_buffer(2 * self.M)
+        co = ctypes.create_string_buffer(k * self.SB) if want_coeffs and k else None
+        inf = ctypes.c_int(0)
+        self._check(self.lib.kzg_gpu_commit_bytes(self.h, _ptr(data), len(data), chunk_size, chunk_offset, co, out,
+                                                  ctypes.byref(inf)), "commit_bytes")
+        return out.raw, bool(inf.value), (co.raw if co is not None else None)
 
     def prove(self, coeffs, first_root, k):
         n = len(coeffs) // self.SB
@@ -435,6 +446,21 @@ class TrustedSetup:
 
     def verify_commit(self, commit, poly):
         return self.create_commit(poly) == commit
+
+    def commit_bytes(self, data, chunk_size=None, byte_offset=0):
+        """kzg-cli's commit_file path (demo/shared/kzg-cli.cpp:41-63) in one device pass: blob::from_bytes(data,
+        byte_offset, len(data), chunk_size) -> poly::from_blob -> create_commit.  Returns (Commit, Poly)."""
+        chunk_size = self.ctx.SB - 1 if chunk_size is None else chunk_size
+        if chunk_size > self.ctx.SB - 1:  # src/blob.cpp:20-25
+            raise ValueError("chunk_size must be at most MAX_CHUNK_BYTES.")
+        if chunk_size < 1 or byte_offset % chunk_size != 0:
+            raise ValueError("byte_offset is not a multiple of chunk_size.")
+        if len(data) % chunk_size != 0:
+            raise ValueError("byte_length is not a multiple of chunk_size.")
+        if len(data) // chunk_size >= self.n:
+            raise ValueError("polynomial degree be at most one less than the setup size (num_coeffs)")
+        xy, inf, coeffs = self.ctx.commit_bytes(bytes(data), chunk_size, byte_offset // chunk_size)
+        return Commit(xy, inf), Poly(self.ctx, coeffs or b"")
 
     def create_proof(self, poly, chunk_offset, chunk_length):
         poly = self._poly(poly)

@@ -131,6 +131,17 @@ def test_demo_cli_flow_cross_process():
         commit = _run(gpu, "commit", "document.txt", cwd=peer).strip()
         assert re.fullmatch(r"[0-9a-f]+", commit)
         assert _run(ref, "commit", "document.txt", cwd=peer, timeout=1200).strip() == commit
+        # the same document through the C ABI's fused device chain (kzg_gpu_commit_bytes), on the CLI-made setup file
+        import sys
+        sys.path.insert(0, os.path.join(ROOT, "kzg-commitments_b200"))
+        import kzg_b200
+        with open(os.path.join(shared, "kzg_public"), "rb") as f:
+            ts = kzg_b200.TrustedSetup.from_file_bytes("bn254", f.read())
+        raw = doc.encode("latin-1")
+        raw += bytes(31 - len(raw) % 31)  # kzg-cli.cpp:50-54
+        fused, _ = ts.commit_bytes(raw, 31)
+        assert fused.serialize().hex() == commit
+        ts.ctx.close()
         for seed in (7, 123456789):
             proof, offset, data = _run(gpu, "prove", "document.txt", seed, cwd=peer).split()
             if seed == 7:  # the reference prover takes seconds per proof: compare one

@@ -417,3 +417,42 @@ def test_prove_batch_equals_single_proofs(ctxs, cname):
         assert infs[3]
     out, infs = ctx.prove_batch(raw, n, [0] * batch, n)
     assert all(infs) and out == bytes(len(out))
+
+
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_commit_bytes_device_chain(ctxs, cname):
+    """SURVEY 8(f) N2: blob::from_bytes -> poly::from_blob -> create_commit chained on the device
+    (kzg_gpu_commit_bytes) against the oracle's blob encoding, interpolation and commitment, against the
+    step-by-step path (Poly.from_blob + create_commit), and the reference's argument errors (src/blob.cpp:20-25)."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    ctx.set_option("precompute", 2)
+    ctx.set_option("window_bits", 0)
+    rng = random.Random(31 + C.id)
+    s = rng.randrange(1, C.r)
+    ts = kzg_b200.TrustedSetup.generate(cname, 5000, s, ctx=ctx)
+    for chunk, k, off in ((ctx.SB - 1, 40, 0), (1, 26, 0), (7, 33, 2), (ctx.SB - 1, 1, 5)):
+        data = bytes(rng.randrange(256) for _ in range(chunk * k))
+        commit, P = ts.commit_bytes(data, chunk, byte_offset=off * chunk)
+        blob = C.blob_from_bytes(data, off * chunk, len(data), chunk)
+        want = C.poly_trim(C.interpolate([x for x, _ in blob], [y for _, y in blob]))
+        assert P.coeffs == want, (chunk, k, off)
+        assert commit.serialize() == C.serialize_g1(C.mul(C.poly_eval(want, s), C.g1)), (chunk, k, off)
+        assert ts.create_commit(kzg_b200.Poly.from_blob(ctx, [y for _, y in blob], off)) == commit
+    # the demo's document shape: 4583 chunks of MAX_CHUNK_BYTES
+    chunk = ctx.SB - 1
+    data = bytes(rng.randrange(32, 127) for _ in range(chunk * 4583))
+    commit, P = ts.commit_bytes(data, chunk)
+    ys = [int.from_bytes(data[i * chunk:(i + 1) * chunk], "little") for i in range(4583)]
+    assert ts.create_commit(kzg_b200.Poly.from_blob(ctx, ys, 0)) == commit
+    assert ctx.poly_eval_range(P.raw + bytes((4583 - len(P)) * ctx.SB), 0, 4583) == C.scalars_to_bytes(ys)
+    q, _, _ = C.poly_quotient(P.coeffs, 100, 4)
+    assert ts.create_proof(P, 100, 4).serialize() == C.serialize_g1(C.mul(C.poly_eval(q, s), C.g1))
+    with pytest.raises(ValueError):
+        ts.commit_bytes(b"x" * ctx.SB, ctx.SB)
+    with pytest.raises(ValueError):
+        ts.commit_bytes(b"x" * 10, 3)
+    with pytest.raises(ValueError):
+        ts.commit_bytes(b"x" * 10, 5, byte_offset=3)
+    c0, p0 = ts.commit_bytes(b"", 4)
+    assert c0.is_inf and len(p0) == 0
