@@ -40,12 +40,15 @@ class _DevBytes:
 
 def gather_partials_device(dist, ctx, device):
     """NCCL all-gather of this rank's projective partial straight from the context's device buffer, then the fold
-    on the device (kzg_gpu_g1_sum_partials_device).  The caller has already waited for the MSM on ctx.stream."""
+    on the device (kzg_gpu_g1_sum_partials_device).  Either the caller has already waited for the MSM on ctx.stream,
+    or it runs this with ctx.stream as torch's current stream, which orders MSM -> all-gather -> fold on the device."""
     import torch
     ptr, nb = ctx.msm_partial_device()
     mine = torch.as_tensor(_DevBytes(ptr, nb), device=device)
     world = dist.get_world_size()
     allp = torch.empty(world * nb, dtype=torch.uint8, device=device)
     dist.all_gather_into_tensor(allp, mine)
-    torch.cuda.current_stream(device).synchronize()
+    cur = torch.cuda.current_stream(device)
+    if cur.cuda_stream != ctx.stream:  # under `with torch.cuda.stream(ExternalStream(ctx.stream))` the fold is already
+        cur.synchronize()              # ordered after the collective on the context's own stream
     return ctx.g1_sum_partials_device(allp, world)
