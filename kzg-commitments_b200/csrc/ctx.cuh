@@ -67,7 +67,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 2;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -596,6 +596,32 @@ struct Ctx final : kzg_gpu_ctx {
                                                                       poly1.as<Fr>());
       LAUNCHED();
       q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
+    } else if (batch == 1 && !d_roots && k <= 4096 && opt_long_division) {
+      // one polynomial, many roots: Z from the product tree (no P part), then CTA-wide long division
+      Fr *pz = nullptr, *zz = nullptr;
+      int rc = enqueue_interpolate(first_root, k, &pz, &zz, false);
+      if (rc) return rc;
+      const uint32_t kk = (uint32_t)k;
+      const size_t smem = (size_t)(kk + 2) * sizeof(Fr);
+      if (opt_long_division >= 2 && kk > 256) {  // 8-CTA cluster, one window element per thread (a cluster step costs
+                                                 // ~1.1 us whatever k is; below 256 roots one CTA steps faster)
+        const unsigned threads = std::max(32u, ((kk + DIV_CLUSTER - 1) / DIV_CLUSTER + 31) / 32 * 32);
+        CK(cudaFuncSetAttribute(poly_long_division_cluster<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        poly_long_division_cluster<C><<<DIV_CLUSTER, threads, smem, stream>>>(n, kk, poly0.as<Fr>(), zz, poly1.as<Fr>());
+      } else {
+        const int ept = kk <= 1024 ? 1 : kk <= 2048 ? 2 : 4;
+        const unsigned threads = ept == 1 ? ((kk + 31) / 32) * 32 : 1024;
+        auto launch = [&](auto kern) -> int {
+          CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          kern<<<1, threads, smem, stream>>>(n, kk, poly0.as<Fr>(), zz, poly1.as<Fr>());
+          return KZG_GPU_OK;
+        };
+        rc = ept == 1 ? launch(poly_long_division<C, 1>) : ept == 2 ? launch(poly_long_division<C, 2>) : launch(poly_long_division<C, 4>);
+        if (rc) return rc;
+      }
+      CK(cudaGetLastError());
+      LAUNCHED();
+      q = poly1.as<Fr>();
     } else {       // many: systolic passes of up to ST roots, ping-ponging between the two buffers
       constexpr int ST = 512, CHK = 256;
       Fr* src = poly0.as<Fr>();
@@ -704,7 +730,7 @@ struct Ctx final : kzg_gpu_ctx {
 
   // interpolation through the consecutive nodes first_x .. first_x + k - 1 of the k values in `stage` (device, SB-byte
   // little-endian each); leaves the interpolant in *p_out (k coefficients) and the vanishing polynomial in *z_out (k + 1)
-  int enqueue_interpolate(int64_t first_x, uint64_t k, Fr** p_out, Fr** z_out) {
+  int enqueue_interpolate(int64_t first_x, uint64_t k, Fr** p_out, Fr** z_out, bool with_p = true) {
     uint64_t kp = 1;
     while (kp < k) kp <<= 1;
     if (inv_fact_n < k) {  // 1/t! table, cached
@@ -720,16 +746,19 @@ struct Ctx final : kzg_gpu_ctx {
     CK(it_za.ensure(2 * kp * sizeof(Fr)));
     CK(it_zb.ensure(2 * kp * sizeof(Fr)));
     CK(qbytes.ensure((kp + 1) * (size_t)SB));
-    interp_scale_values<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(
-        k, stage.as<uint8_t>(), inv_fact.as<Fr>(), it_u.as<Fr>());
-    LAUNCHED();
+    if (with_p) {
+      interp_scale_values<C><<<(unsigned)std::min<uint64_t>((k + 127) / 128, 148 * 8), 128, 0, stream>>>(
+          k, stage.as<uint8_t>(), inv_fact.as<Fr>(), it_u.as<Fr>());
+      LAUNCHED();
+    }
     Fr *pin = it_pa.as<Fr>(), *pout = it_pb.as<Fr>(), *zin = it_za.as<Fr>(), *zout = it_zb.as<Fr>();
     interp_leaves<C><<<(unsigned)std::min<uint64_t>((kp + 3) / 4, 148 * 16), 128, 0, stream>>>(
-        k, kp, (long long)first_x, it_u.as<Fr>(), inv_fact.as<Fr>(), pin, zin);
+        k, kp, (long long)first_x, it_u.as<Fr>(), inv_fact.as<Fr>(), pin, zin, with_p ? 1 : 0);
     LAUNCHED();
     for (uint64_t m = 1; m < kp; m <<= 1) {
-      const uint64_t npairs = kp / (2 * m), warps = npairs * (4 * m + 1);
-      interp_tree_level<C><<<(unsigned)std::min<uint64_t>((warps + 3) / 4, 148 * 32), 128, 0, stream>>>(m, npairs, pin, zin, pout, zout);
+      const uint64_t npairs = kp / (2 * m), warps = npairs * ((with_p ? 4 : 2) * m + 1);
+      interp_tree_level<C><<<(unsigned)std::min<uint64_t>((warps + 3) / 4, 148 * 32), 128, 0, stream>>>(m, npairs, pin, zin, pout, zout,
+                                                                                                        with_p ? 1 : 0);
       LAUNCHED();
       std::swap(pin, pout);
       std::swap(zin, zout);

@@ -11,6 +11,9 @@
 // Coefficients travel as little-endian SCALAR_BYTES records (BytesFromZZ layout, src/util.cpp:31-43)
 // and are held in Montgomery form on device.  BN curves have 2-adicity 2, so nothing here uses an NTT.
 #pragma once
+#if defined(__CUDACC__)
+#include <cooperative_groups.h>
+#endif
 #include "field.cuh"
 
 namespace kzgb200 {
@@ -282,14 +285,14 @@ template <class C>
 __global__ void __launch_bounds__(128)
 interp_leaves(uint64_t k, uint64_t kp, long long first_x, const Field<typename C::FrP>* __restrict__ u,
               const Field<typename C::FrP>* __restrict__ inv_fact, Field<typename C::FrP>* __restrict__ P0,
-              Field<typename C::FrP>* __restrict__ Z0) {
+              Field<typename C::FrP>* __restrict__ Z0, int with_p) {
   using Fr = Field<typename C::FrP>;
   const int lane = threadIdx.x & 31;
   const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
   const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   for (uint64_t j = warp; j < kp; j += nwarps) {
     Fr acc = Fr::zero();
-    if (j < k) {
+    if (with_p && j < k) {
       for (uint64_t i = lane; i <= j; i += 32) {
         const Fr term = Fr::mul(u[i], inv_fact[j - i]);
         acc = ((j - i) & 1) ? Fr::sub(acc, term) : Fr::add(acc, term);
@@ -297,7 +300,7 @@ interp_leaves(uint64_t k, uint64_t kp, long long first_x, const Field<typename C
     }
     acc = warp_sum_field<Fr>(acc);
     if (lane == 0) {
-      P0[j] = acc;
+      if (with_p) P0[j] = acc;
       if (j < k) {
         Z0[2 * j] = Fr::neg(fr_from_i64<C>(first_x + (long long)j));
         Z0[2 * j + 1] = Fr::one();
@@ -317,16 +320,17 @@ template <class C>
 __global__ void __launch_bounds__(128)
 interp_tree_level(uint64_t m, uint64_t npairs, const Field<typename C::FrP>* __restrict__ Pin,
                   const Field<typename C::FrP>* __restrict__ Zin, Field<typename C::FrP>* __restrict__ Pout,
-                  Field<typename C::FrP>* __restrict__ Zout) {
+                  Field<typename C::FrP>* __restrict__ Zout, int with_p) {
   using Fr = Field<typename C::FrP>;
   const int lane = threadIdx.x & 31;
   const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
   const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-  const uint64_t per_pair = 4 * m + 1;  // 2m outputs of P, 2m + 1 of Z
+  const uint64_t p_outs = with_p ? 2 * m : 0;
+  const uint64_t per_pair = p_outs + 2 * m + 1;  // 2m outputs of P (when wanted), 2m + 1 of Z
   for (uint64_t w = warp; w < npairs * per_pair; w += nwarps) {
     const uint64_t q = w / per_pair, o = w - q * per_pair;
-    const bool is_z = o >= 2 * m;
-    const uint64_t i = is_z ? o - 2 * m : o;
+    const bool is_z = o >= p_outs;
+    const uint64_t i = is_z ? o - p_outs : o;
     const Fr* ZL = Zin + (2 * q) * (m + 1);
     const Fr* R = is_z ? Zin + (2 * q + 1) * (m + 1) : Pin + (2 * q + 1) * m;
     const uint64_t rlen = is_z ? m + 1 : m;
@@ -339,6 +343,109 @@ interp_tree_level(uint64_t m, uint64_t npairs, const Field<typename C::FrP>* __r
       else Pout[q * (2 * m) + i] = (i < m) ? Fr::add(acc, Pin[(2 * q) * m + i]) : acc;
     }
   }
+}
+
+// q = P div Z for a monic Z of degree k (Z = prod (x - x_i), from the product tree above), one CTA:
+// schoolbook long division with the k-coefficient active window of the remainder held in registers.
+// Coefficient index m of the remainder lives on residue m mod k (thread = residue mod T, slot = residue / T),
+// so no value ever moves between threads: at step i (quotient index, downwards) the owner of index i + k holds
+// a finished coefficient = q_i, publishes it through shared memory, takes P[i] as its new element, and every
+// element m in [i, i + k) subtracts q_i * z_{m-i}.  One barrier and one (EPT independent) modmul per step,
+// n - k steps — against (n + 512) steps per pass of 512 roots for the systolic form.
+template <class C, int EPT>
+__global__ void __launch_bounds__(1024)
+poly_long_division(uint64_t n, uint32_t k, const Field<typename C::FrP>* __restrict__ P,
+                   const Field<typename C::FrP>* __restrict__ Z, Field<typename C::FrP>* __restrict__ q) {
+  using Fr = Field<typename C::FrP>;
+  extern __shared__ __align__(16) uint8_t division_smem[];
+  Fr* zs = reinterpret_cast<Fr*>(division_smem);  // z_0 .. z_{k-1}
+  Fr* qs = zs + k;                                // q_i, double-buffered
+  const uint32_t t = threadIdx.x, T = blockDim.x;
+  for (uint32_t j = t; j < k; j += T) zs[j] = Z[j];
+  Fr r[EPT];
+  const uint64_t base = n - k;  // the window starts as the top k coefficients
+#pragma unroll
+  for (int e = 0; e < EPT; e++) {
+    const uint32_t res = t + (uint32_t)e * T;
+    r[e] = Fr::zero();
+    if (res < k) r[e] = P[base + (uint64_t)((res + k - (uint32_t)(base % k)) % k)];
+  }
+  __syncthreads();
+  uint32_t own = (uint32_t)((n - 1) % k);  // residue of index i + k for i = n - k - 1
+  for (int64_t i = (int64_t)(n - k) - 1; i >= 0; i--) {
+    if (own % T == t) {
+      const uint32_t slot = own / T;
+#pragma unroll
+      for (int e = 0; e < EPT; e++)
+        if ((uint32_t)e == slot) {
+          qs[i & 1] = r[e];
+          q[i] = r[e];
+          r[e] = P[i];
+        }
+    }
+    __syncthreads();
+    const Fr qq = qs[i & 1];
+#pragma unroll
+    for (int e = 0; e < EPT; e++) {
+      const uint32_t res = t + (uint32_t)e * T;
+      if (res < k) {
+        const uint32_t j = res >= own ? res - own : res + k - own;  // m - i for the index m = res (mod k) in the window
+        r[e] = Fr::sub(r[e], Fr::mul(qq, zs[j]));
+      }
+    }
+    own = own == 0 ? k - 1 : own - 1;
+  }
+}
+
+// The same long division on a thread-block CLUSTER of 8 CTAs: the window of k coefficients is spread over
+// 8 SMs (one element per thread, residue = cluster-wide thread index), every CTA keeps its own copy of Z in
+// shared memory, and the owner of the finished coefficient writes q_i into all 8 CTAs' shared memory
+// through DSMEM before the per-step cluster barrier.  A step is then one modmul deep (~0.4 us) plus the
+// barrier (~0.2 us) instead of k modmuls queued on one SM's multiplier pipe.
+constexpr int DIV_CLUSTER = 8;
+template <class C>
+__global__ void __cluster_dims__(DIV_CLUSTER, 1, 1) __launch_bounds__(512)
+poly_long_division_cluster(uint64_t n, uint32_t k, const Field<typename C::FrP>* __restrict__ P,
+                           const Field<typename C::FrP>* __restrict__ Z, Field<typename C::FrP>* __restrict__ q) {
+  namespace cg = cooperative_groups;
+  using Fr = Field<typename C::FrP>;
+  extern __shared__ __align__(16) uint8_t division_smem[];
+  Fr* zs = reinterpret_cast<Fr*>(division_smem);
+  Fr* qs = zs + k;
+  cg::cluster_group cluster = cg::this_cluster();
+  const uint32_t t = threadIdx.x, T = blockDim.x;
+  const uint32_t res = cluster.block_rank() * T + t;  // the residue (index mod k) this thread owns
+  for (uint32_t j = t; j < k; j += T) zs[j] = Z[j];
+  Fr* remote_qs[DIV_CLUSTER];
+#pragma unroll
+  for (int c = 0; c < DIV_CLUSTER; c++) remote_qs[c] = cluster.map_shared_rank(qs, c);
+  const uint64_t base = n - k;
+  Fr r = Fr::zero(), nxt = Fr::zero();
+  if (res < k) {
+    r = P[base + (uint64_t)((res + k - (uint32_t)(base % k)) % k)];
+    // the element this thread takes over when it first owns the finished coefficient (step i = res mod k),
+    // loaded now and refreshed k steps ahead each time, so no global-load latency sits on the step's critical path
+    const uint64_t d = ((base - 1) % k + k - res) % k;
+    if (base >= 1 + d) nxt = P[base - 1 - d];
+  }
+  cluster.sync();
+  uint32_t own = (uint32_t)((n - 1) % k);
+  for (int64_t i = (int64_t)(n - k) - 1; i >= 0; i--) {
+    if (own == res) {
+#pragma unroll
+      for (int c = 0; c < DIV_CLUSTER; c++) remote_qs[c][i & 1] = r;
+      q[i] = r;
+      r = nxt;
+      if (i >= (int64_t)k) nxt = P[i - (int64_t)k];
+    }
+    cluster.sync();
+    if (res < k) {
+      const uint32_t j = res >= own ? res - own : res + k - own;
+      r = Fr::sub(r, Fr::mul(qs[i & 1], zs[j]));
+    }
+    own = own == 0 ? k - 1 : own - 1;
+  }
+  cluster.sync();  // no CTA exits while a peer may still write into its shared memory
 }
 
 }  // namespace kzgb200

@@ -298,17 +298,28 @@ def test_msm_2_16_linearity_and_oracle(ctxs):
 
 @pytest.mark.parametrize("cname", CURVE_NAMES)
 def test_quotient_many_roots_systolic(ctxs, cname):
-    """A6 with many opened points (multi-proof rows of benchmark.cpp): the systolic kernel, one pass (k = 64, 512),
-    chained passes (k = 700, 1300) and the boundary with the scan kernel (k = 47, 48), against the oracle."""
+    """A6 with many opened points (multi-proof rows of benchmark.cpp), against the oracle: the CTA-wide long
+    division by Z on an 8-CTA cluster (default for one polynomial, option long_division = 2) and on one CTA
+    (= 1; 1, 2 and 4 window elements per thread), and the systolic kernel (= 0; one pass k = 64, 512, chained passes k = 700, 1300), plus the boundary with the
+    scan kernel (k = 47, 48)."""
     C = get_curve(cname)
     ctx = ctxs(cname)
     rng = random.Random(77 + C.id)
     n = 1501
     coeffs = [rng.randrange(C.r) for _ in range(n)]
     raw = C.scalars_to_bytes(coeffs)
-    for off, k in ((0, 47), (0, 48), (3, 64), (10, 512), (1, 700), (5, 1300), (0, 1500)):
-        q, _, _ = C.poly_quotient(coeffs, off, k)
-        assert ctx.poly_quotient(raw, off, k) == C.scalars_to_bytes(q), (off, k)
+    for long_division in (2, 1, 0):
+        ctx.set_option("long_division", long_division)
+        for off, k in ((0, 47), (0, 48), (3, 64), (10, 512), (1, 700), (5, 1300), (0, 1500)):
+            q, _, _ = C.poly_quotient(coeffs, off, k)
+            assert ctx.poly_quotient(raw, off, k) == C.scalars_to_bytes(q), (long_division, off, k)
+    n2 = 2600  # 2 and 4 window elements per thread (k > 1024, k > 2048), window not a multiple of the CTA size
+    coeffs2 = [rng.randrange(C.r) for _ in range(n2)]
+    for off, k in ((2, 1025), (0, 2048), (7, 2100)):
+        q, _, _ = C.poly_quotient(coeffs2, off, k)
+        for long_division in (1, 2):
+            ctx.set_option("long_division", long_division)
+            assert ctx.poly_quotient(C.scalars_to_bytes(coeffs2), off, k) == C.scalars_to_bytes(q), (long_division, off, k)
     # proof through the chained path equals [q(s)]G
     s = rng.randrange(C.r)
     ts = kzg_b200.TrustedSetup.generate(cname, n + 1, s, ctx=ctx)
