@@ -362,14 +362,16 @@ bool kzg::trusted_setup::verify_proof(kzg::commit& commit, kzg::proof& proof, kz
 
   ECP2 z_s = polyeval_G2(vanish);                     // device
   ECP i_s = polyeval_G1(interp);                      // device
-  FP12 lhs, rhs;
-  PAIR_ate(&lhs, &z_s, &proof.get_curve_point());     // e([Z(s)]_2, proof)
-  PAIR_fexp(&lhs);
-  ECP_neg(&i_s);
-  ECP_add(&i_s, &commit.get_curve_point());           // commit - [I(s)]_1
-  PAIR_ate(&rhs, &_G2[0], &i_s);
-  PAIR_fexp(&rhs);
-  return FP12_equals(&lhs, &rhs);
+  // The reference compares fexp(ate(Z2, proof)) with fexp(ate(G2, commit - I1)) (src/trusted_setup.cpp:242-253): two
+  // Miller loops and two final exponentiations.  Same predicate, one shared Miller loop and ONE final
+  // exponentiation: e(Z2, proof) * e(G2, I1 - commit) == 1.
+  ECP d = commit.get_curve_point();
+  ECP_neg(&d);
+  ECP_add(&d, &i_s);                                  // [I(s)]_1 - commit
+  FP12 acc;
+  PAIR_double_ate(&acc, &z_s, &proof.get_curve_point(), &_G2[0], &d);
+  PAIR_fexp(&acc);
+  return FP12_isunity(&acc);
 }
 
 void kzg::trusted_setup::export_setup(const std::string& filename) {
