@@ -359,7 +359,11 @@ def run_b200(args):
                     "ms_per_step": total_e2e_ms / args.steps},
             "gpu_launches": gpu_launches,
             "roofline": {"bound": "int32-imad", "kernel": "msm_accumulate", "achieved": achieved / 1e12, "peak": peak / 1e12,
-                         "unit": "TIMAD/s", "frac": achieved / peak, "traffic": None,
+                         "unit": "TIMAD/s", "frac": achieved / peak,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one msm_accumulate launch at this workload from
+                         # the ncu --set full capture summarised in profiles/r1i_accumulate_ncu.md (2.734 + 0.304 GB)
+                         "traffic": 3.038e9 if (args.log2n == 20 and args.precompute == 1 and not args.window_bits) else None,
+                         "traffic_unit": "bytes/launch", "algorithmic_bytes_per_launch": stats["records"] * 96 + stats["records"] * 4,
                          "kernel_ms": acc_ms, "kernel_share_of_step": acc_ms / ms_per_step,
                          "records_per_launch": stats["records"], "imad_per_record": 10 * imad_per_modmul,
                          "peak_source": "nominal: 64 IMAD-class slots/clk/SM x 148 SMs x sm_max_mhz (IMAD.WIDE = 2 slots)",

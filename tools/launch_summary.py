@@ -5,8 +5,10 @@ from collections import OrderedDict
 rows = [l for l in open(sys.argv[1]) if l.startswith('"')]
 r = list(csv.reader(rows))
 hdr = r[0]; ki = hdr.index('Kernel Name'); vi = hdr.index('Metric Value'); ui = hdr.index('Metric Unit')
-ks = [(re.sub(r'^void ', '', re.sub(r'[<(].*', '', x[ki])), float(x[vi].replace(',', '')) / (1000 if x[ui] == 'ns' else 1)) for x in r[1:]]
+ks = [(re.sub(r'^void ', '', re.sub(r'[<(].*', '', x[ki])).split('::')[-1], float(x[vi].replace(',', '')) / (1000 if x[ui] == 'ns' else 1)) for x in r[1:]]
 last = [i for i, k in enumerate(ks) if k[0] == 'msm_digits'][-1]
+end = next(i for i in range(last, len(ks)) if ks[i][0] == 'msm_finish') + 1
+ks = ks[:end]
 agg = OrderedDict(); tot = 0
 for n, v in ks[last:]:
     a = agg.setdefault(n, [0, 0]); a[0] += v; a[1] += 1; tot += v
