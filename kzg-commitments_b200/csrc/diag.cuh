@@ -68,8 +68,8 @@ __global__ void __launch_bounds__(256) bench_modmul(int iters, uint32_t seed, ui
   x.v[0] ^= (seed * (tid + 1)) & 0xffff;
   z.v[0] ^= (seed * (tid + 7)) & 0xffff;
   for (int it = 0; it < iters; it++) {
-    x = F::mul_inline(x, y);
-    z = F::mul_inline(z, y);
+    x = F::mul_best_inline(x, y);
+    z = F::mul_best_inline(z, y);
   }
   uint32_t o = 0;
 #pragma unroll
@@ -107,6 +107,14 @@ KZG_HDN int check_field(Lcg& g) {
   bad += !(F::to_mont(F::from_mont(a)) == a);
   if (!a.is_zero()) bad += !(F::mul(a, F::inv(a)) == F::one());
   bad += !(F::inv(a) == F::inv_fermat(a));  // binary-GCD inverse against the Fermat ladder
+  // the Karatsuba / separated-reduction product (field.cuh, KZG_KARATSUBA) against the interleaved one
+  if constexpr (F::L % 4 == 0) {
+    const F m1 = F::neg(F::one());
+    bad += !(F::mul_karatsuba_inline(a, b) == F::mul_inline(a, b));
+    bad += !(F::mul_karatsuba_inline(a, a) == F::mul_inline(a, a));
+    bad += !(F::mul_karatsuba_inline(m1, m1) == F::mul_inline(m1, m1));
+    bad += !(F::mul_karatsuba_inline(F::r2(), m1) == F::mul_inline(F::r2(), m1));
+  }
   return bad;
 }
 

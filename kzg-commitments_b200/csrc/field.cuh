@@ -16,6 +16,13 @@
 
 namespace kzgb200 {
 
+// 1 = mul() runs the Karatsuba / separated-reduction product where L % 4 == 0.  Measured on B200 (profiles/r1j):
+// 12 % fewer wide multiplications but the same 30.9 G modmul/s and the same msm_accumulate time as the interleaved
+// product, at 20 more registers — so the interleaved form stays the default and this one stays as a checked variant.
+#ifndef KZG_KARATSUBA
+#define KZG_KARATSUBA 0
+#endif
+
 template <class P>
 struct alignas((P::L % 4 == 0) ? 16 : 8) Field {  // aligned for 128-bit (64-bit for 6 limbs) loads and stores
   static constexpr int L = P::L;
@@ -98,7 +105,23 @@ struct alignas((P::L % 4 == 0) ? 16 : 8) Field {  // aligned for 128-bit (64-bit
   // bound (ncu: stall_no_instruction 4.3 of 9.4 cycles per issue, profiles/r1_accumulate_v1.md);
   // with the call the hot loop fits the instruction cache.  mul_inline() is the same body for
   // call sites that want it fused (the modmul microbenchmark).
-  KZG_HDN static Field mul(Field a, Field b) { return mul_inline(a, b); }
+  KZG_HDN static Field mul(Field a, Field b) {
+#if KZG_KARATSUBA
+    if constexpr (L % 4 == 0) return mul_karatsuba_inline(a, b);
+    else return mul_inline(a, b);
+#else
+    return mul_inline(a, b);
+#endif
+  }
+  // the body mul() uses, for call sites that want it fused (the modmul microbenchmark)
+  KZG_HD static Field mul_best_inline(const Field& a, const Field& b) {
+#if KZG_KARATSUBA
+    if constexpr (L % 4 == 0) return mul_karatsuba_inline(a, b);
+    else return mul_inline(a, b);
+#else
+    return mul_inline(a, b);
+#endif
+  }
   KZG_HD static Field mul_inline(const Field& a, const Field& b) {
     static_assert(L % 2 == 0, "even limb count required");
     uint32_t ev[L], od[L];
@@ -128,6 +151,150 @@ struct alignas((P::L % 4 == 0) ? 16 : 8) Field {  // aligned for 128-bit (64-bit
     cond_sub_p(r);
     return r;
   }
+  // ---- Karatsuba / separated-operand-scanning form of the same product (L divisible by 4).
+  // The heavy integer-multiply pipe is the bound of every hot kernel (ncu: 93.6 % active in msm_accumulate,
+  // profiles/r1i), while two thirds of the issue slots are idle.  One level of Karatsuba on the L x L
+  // product trades L^2/4 wide multiplications (of 2L^2 + L) for ~6L additions, which run on the other
+  // integer pipe:  a*b = z0 + ((al+ah)(bl+bh) - z0 - z2) 2^(16L) + z2 2^(32L),  three H x H products, H = L/2.
+  // The Montgomery reduction then works on the low L words alone (L rows of m*p with two carry chains per
+  // row on absolute-position accumulators) and the high L words are added at the end:
+  //   (t + M p)/R = t_high + (t_low + M p)/R,   t_high < p,  (t_low + M p)/R <= p.
+  static constexpr int H = L / 2;
+  // z[0..2H) = x[0..H) * y[0..H); even and odd columns of x accumulate into two absolute-position arrays so every
+  // row is two independent carry chains of fused multiply-adds
+  KZG_HD static void mul_half(const uint32_t* x, const uint32_t* y, uint32_t* z) {
+    uint32_t E[2 * H + 2], O[2 * H + 2];
+#pragma unroll
+    for (int k = 0; k < 2 * H + 2; k++) { E[k] = 0; O[k] = 0; }
+#pragma unroll
+    for (int j = 0; j < H; j += 2) {  // row 0
+      E[j] = ptx::mul_lo(x[j], y[0]);
+      E[j + 1] = ptx::mul_hi(x[j], y[0]);
+      O[j + 1] = ptx::mul_lo(x[j + 1], y[0]);
+      O[j + 2] = ptx::mul_hi(x[j + 1], y[0]);
+    }
+#pragma unroll
+    for (int i = 1; i < H; i++) {
+      // a product landing on words (q, q + 1) goes to E when q is even and to O when q is odd: every accumulator
+      // word pair then stays one aligned 64-bit register pair for the fused wide multiply-add in all rows
+      uint32_t* A = (i & 1) ? O : E;  // even columns of x: q = i + j has the parity of i
+      uint32_t* B = (i & 1) ? E : O;  // odd columns
+      const uint32_t yi = y[i];
+      A[i] = ptx::mad_lo_cc(x[0], yi, A[i]);
+      A[i + 1] = ptx::madc_hi_cc(x[0], yi, A[i + 1]);
+#pragma unroll
+      for (int j = 2; j < H; j += 2) {
+        A[i + j] = ptx::madc_lo_cc(x[j], yi, A[i + j]);
+        A[i + j + 1] = ptx::madc_hi_cc(x[j], yi, A[i + j + 1]);
+      }
+      A[i + H] = ptx::addc(A[i + H], 0);  // holds at most the previous row's carry
+      B[i + 1] = ptx::mad_lo_cc(x[1], yi, B[i + 1]);
+      B[i + 2] = ptx::madc_hi_cc(x[1], yi, B[i + 2]);
+#pragma unroll
+      for (int j = 3; j < H; j += 2) {
+        B[i + j] = ptx::madc_lo_cc(x[j], yi, B[i + j]);
+        B[i + j + 1] = ptx::madc_hi_cc(x[j], yi, B[i + j + 1]);
+      }
+      B[i + H + 1] = ptx::addc(B[i + H + 1], 0);
+    }
+    z[0] = E[0];
+    z[1] = ptx::add_cc(E[1], O[1]);
+#pragma unroll
+    for (int k = 2; k < 2 * H - 1; k++) z[k] = ptx::addc_cc(E[k], O[k]);
+    z[2 * H - 1] = ptx::addc(E[2 * H - 1], O[2 * H - 1]);
+  }
+
+  // t[0..2L) = a * b
+  KZG_HD static void mul_wide_karatsuba(const Field& a, const Field& b, uint32_t* t) {
+    uint32_t sa[H], sb[H], mid[2 * H + 1];
+    mul_half(a.v, b.v, t);               // z0
+    mul_half(a.v + H, b.v + H, t + L);   // z2
+    sa[0] = ptx::add_cc(a.v[0], a.v[H]);
+#pragma unroll
+    for (int k = 1; k < H; k++) sa[k] = ptx::addc_cc(a.v[k], a.v[H + k]);
+    const uint32_t ca = ptx::addc(0, 0);
+    sb[0] = ptx::add_cc(b.v[0], b.v[H]);
+#pragma unroll
+    for (int k = 1; k < H; k++) sb[k] = ptx::addc_cc(b.v[k], b.v[H + k]);
+    const uint32_t cb = ptx::addc(0, 0);
+    mul_half(sa, sb, mid);               // (sa mod 2^(32H)) (sb mod 2^(32H))
+    const uint32_t ma = 0u - ca, mb = 0u - cb;
+    // + ca * sb * 2^(32H) + cb * sa * 2^(32H) + ca cb 2^(64H)
+    mid[H] = ptx::add_cc(mid[H], sb[0] & ma);
+#pragma unroll
+    for (int k = 1; k < H; k++) mid[H + k] = ptx::addc_cc(mid[H + k], sb[k] & ma);
+    mid[2 * H] = ptx::addc(ca & cb, 0);
+    mid[H] = ptx::add_cc(mid[H], sa[0] & mb);
+#pragma unroll
+    for (int k = 1; k < H; k++) mid[H + k] = ptx::addc_cc(mid[H + k], sa[k] & mb);
+    mid[2 * H] = ptx::addc(mid[2 * H], 0);
+    // - z0 - z2   (the result a_l b_h + a_h b_l is non-negative and below 2^(64H + 1))
+    mid[0] = ptx::sub_cc(mid[0], t[0]);
+#pragma unroll
+    for (int k = 1; k < 2 * H; k++) mid[k] = ptx::subc_cc(mid[k], t[k]);
+    mid[2 * H] = ptx::subc(mid[2 * H], 0);
+    mid[0] = ptx::sub_cc(mid[0], t[L]);
+#pragma unroll
+    for (int k = 1; k < 2 * H; k++) mid[k] = ptx::subc_cc(mid[k], t[L + k]);
+    mid[2 * H] = ptx::subc(mid[2 * H], 0);
+    // t += mid * 2^(32H)
+    t[H] = ptx::add_cc(t[H], mid[0]);
+#pragma unroll
+    for (int k = 1; k <= 2 * H; k++) t[H + k] = ptx::addc_cc(t[H + k], mid[k]);
+#pragma unroll
+    for (int k = 3 * H + 1; k < 2 * L - 1; k++) t[k] = ptx::addc_cc(t[k], 0);
+    t[2 * L - 1] = ptx::addc(t[2 * L - 1], 0);
+  }
+
+  // Montgomery reduction of t[0..2L) (t < p^2... any t < p * 2^(32L)) to the canonical residue t / R mod p
+  KZG_HD static Field mont_reduce_wide(const uint32_t* t) {
+    uint32_t E[2 * L + 2], O[2 * L + 2];
+#pragma unroll
+    for (int k = 0; k < 2 * L + 2; k++) { E[k] = k < L ? t[k] : 0u; O[k] = 0; }
+#pragma unroll
+    for (int i = 0; i < L; i++) {
+      // complete word at position i; its carry enters the odd-column chain at position i + 1.  Accumulator choice
+      // by the parity of the product's low word position, as in mul_half (keeps 64-bit register pairs aligned).
+      uint32_t* A = (i & 1) ? O : E;
+      uint32_t* B = (i & 1) ? E : O;
+      A[i] = ptx::add_cc(A[i], B[i]);
+      const uint32_t m = ptx::mul_lo(A[i], P::INV);
+      B[i + 1] = ptx::madc_lo_cc(P::mod(1), m, B[i + 1]);
+      B[i + 2] = ptx::madc_hi_cc(P::mod(1), m, B[i + 2]);
+#pragma unroll
+      for (int j = 3; j < L; j += 2) {
+        B[i + j] = ptx::madc_lo_cc(P::mod(j), m, B[i + j]);
+        B[i + j + 1] = ptx::madc_hi_cc(P::mod(j), m, B[i + j + 1]);
+      }
+      B[i + L + 1] = ptx::addc(B[i + L + 1], 0);
+      A[i] = ptx::mad_lo_cc(P::mod(0), m, A[i]);  // == 0 by the choice of m; only its carry is wanted
+      A[i + 1] = ptx::madc_hi_cc(P::mod(0), m, A[i + 1]);
+#pragma unroll
+      for (int j = 2; j < L; j += 2) {
+        A[i + j] = ptx::madc_lo_cc(P::mod(j), m, A[i + j]);
+        A[i + j + 1] = ptx::madc_hi_cc(P::mod(j), m, A[i + j + 1]);
+      }
+      A[i + L] = ptx::addc(A[i + L], 0);
+    }
+    Field r;
+    r.v[0] = ptx::add_cc(E[L], O[L]);
+#pragma unroll
+    for (int k = 1; k < L - 1; k++) r.v[k] = ptx::addc_cc(E[L + k], O[L + k]);
+    r.v[L - 1] = ptx::addc(E[2 * L - 1], O[2 * L - 1]);
+    r.v[0] = ptx::add_cc(r.v[0], t[L]);
+#pragma unroll
+    for (int k = 1; k < L - 1; k++) r.v[k] = ptx::addc_cc(r.v[k], t[L + k]);
+    r.v[L - 1] = ptx::addc(r.v[L - 1], t[2 * L - 1]);
+    cond_sub_p(r);
+    return r;
+  }
+
+  KZG_HD static Field mul_karatsuba_inline(const Field& a, const Field& b) {
+    uint32_t t[2 * L];
+    mul_wide_karatsuba(a, b, t);
+    return mont_reduce_wide(t);
+  }
+
   KZG_HD static Field sqr(const Field& a) { return mul(a, a); }
 
   // R^2 is the row operand so that ANY 32L-bit input (not only canonical ones) comes out canonical:

@@ -367,7 +367,7 @@ msm_task_place(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts
   }
 }
 template <class F>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, sizeof(F) <= 48 ? 4 : 1)
 msm_accumulate(const uint32_t* __restrict__ ntasks_ptr, const MsmTask* __restrict__ tasks,
                const uint32_t* __restrict__ sorted, const Affine<F>* __restrict__ bases, XYZZ<F>* __restrict__ partial) {
   const uint32_t ntasks = *ntasks_ptr;
