@@ -159,7 +159,10 @@ struct Ctx final : kzg_gpu_ctx {
 
   // ------------------------------------------------------------------ SRS
   // window width of the per-SRS table: minimise  n*W*10 + 2^(c-1)*30  modmuls (mixed adds + bucket
-  // reduction) for an MSM over the whole SRS, subject to W <= MAXW and a table-size budget.
+  // reduction) for an MSM over the whole SRS, subject to W <= MAXW and a table-size budget.  A width whose
+  // LAST window holds only a few scalar bits sends n / 2^(bits-1) records to each of a handful of buckets:
+  // their histogram atomics serialise (measured 0.27 ms for 2048 records per bucket at n = 2^14, c = 14) and
+  // their task lists need deep folds, so that pile-up is charged at ~3800 modmul-equivalents per record.
   int pick_table_c(uint64_t n) const {
     if (opt_window_bits) return opt_window_bits;
     int best = 0;
@@ -168,7 +171,9 @@ struct Ctx final : kzg_gpu_ctx {
       const int W = (C::SCALAR_BITS + 1 + c - 1) / c;
       if (W > MAXW) continue;
       if ((double)W * n * sizeof(Affine<Fp>) > 24e9) continue;
-      const double cost = (double)n * W * 10.0 + (double)(1ull << (c - 1)) * 30.0;
+      const int top_bits = C::SCALAR_BITS + 1 - (W - 1) * c;  // >= 1
+      const double pile = (double)n / (double)(1ull << (top_bits - 1));
+      const double cost = (double)n * W * 10.0 + (double)(1ull << (c - 1)) * 30.0 + 3800.0 * pile;
       if (!best || cost < best_cost) { best = c; best_cost = cost; }
     }
     return best ? best : 8;
