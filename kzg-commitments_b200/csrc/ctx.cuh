@@ -178,6 +178,21 @@ struct Ctx final : kzg_gpu_ctx {
     }
     return best ? best : 8;
   }
+  // window width without the table (every window has its own bucket group and the finish does the doublings):
+  // the same cost model with W bucket groups to reduce
+  int pick_plain_c(uint64_t count) const {
+    if (count < 32) return 4;
+    int best = 8;
+    double best_cost = 0;
+    for (int c = 6; c <= 16; c++) {
+      const int W = (C::SCALAR_BITS + 1 + c - 1) / c;
+      const int top_bits = C::SCALAR_BITS + 1 - (W - 1) * c;
+      const double pile = (double)count / (double)(1ull << (top_bits - 1));
+      const double cost = (double)count * W * 10.0 + (double)W * (double)(1ull << (c - 1)) * 30.0 + 3800.0 * pile;
+      if (best_cost == 0 || cost < best_cost) { best = c; best_cost = cost; }
+    }
+    return best;
+  }
   int build_table() {
     g1_table.release();
     g2_table.release();
@@ -272,8 +287,7 @@ struct Ctx final : kzg_gpu_ctx {
                   uint64_t batch, uint64_t base_offset) {
     MsmShape sh;
     const bool precomp = table != nullptr;
-    sh.c = precomp ? tc : (opt_window_bits ? opt_window_bits : std::min(16, std::max(8, ilog2(count) - 4)));
-    if (count < 32 && !precomp && !opt_window_bits) sh.c = 4;
+    sh.c = precomp ? tc : (opt_window_bits ? opt_window_bits : pick_plain_c(count));
     sh.W = (C::SCALAR_BITS + 1 + sh.c - 1) / sh.c;
     sh.nb = 1 << (sh.c - 1);
     sh.precomp = precomp ? 1 : 0;
@@ -452,9 +466,14 @@ struct Ctx final : kzg_gpu_ctx {
       msm_group_combine<F><<<(unsigned)((groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
     LAUNCHED();
     phase_mark(3);
-    msm_finish<F><<<(unsigned)((batch + 31) / 32), 32, 0, stream>>>(
-        batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
-        out_xyzz.as<XYZZ<F>>());
+    if (opt_team && sh.groups_per_msm > 1 && batch <= TEAM_MAX_ITEMS)  // Horner over the windows: a long dependent chain
+      msm_finish_team<F><<<(unsigned)((4 * batch + 127) / 128), 128, 0, stream>>>(
+          batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
+          out_xyzz.as<XYZZ<F>>());
+    else
+      msm_finish<F><<<(unsigned)((batch + 31) / 32), 32, 0, stream>>>(
+          batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
+          out_xyzz.as<XYZZ<F>>());
     LAUNCHED();
     phase_mark(4);
     last_batch = batch;

@@ -203,5 +203,32 @@ msm_group_combine_team(uint64_t groups, int h, const XYZZ<F>* __restrict__ t1, c
   }
 }
 
+// msm_finish with the Horner chain over the windows (no table: W - 1 rounds of c doublings + one addition, all
+// dependent) on a team; lane 0 then normalises and writes the bytes as msm_finish_thread does.
+template <class F>
+__global__ void __launch_bounds__(128)
+msm_finish_team(uint64_t batch, int groups_per_msm, int c, const XYZZ<F>* __restrict__ group_out,
+                uint8_t* __restrict__ out_bytes, int* __restrict__ is_inf, int modbytes, XYZZ<F>* __restrict__ out_xyzz) {
+  KZG_TEAM_LOOP(m, batch) {
+    XYZZ<F> acc = group_out[m * groups_per_msm + (groups_per_msm - 1)];
+    for (int g = groups_per_msm - 2; g >= 0; g--) {
+      for (int k = 0; k < c; k++) acc = team_dbl<F>(acc);
+      const XYZZ<F> v = group_out[m * groups_per_msm + g];
+      acc = team_add<F>(acc, v);
+    }
+    if ((threadIdx.x & 3) == 0) {
+      if (out_xyzz) out_xyzz[m] = acc;
+      const int nbytes = CoordCount<F>::value * modbytes;
+      if (acc.is_inf()) {
+        for (int j = 0; j < nbytes; j++) out_bytes[m * nbytes + j] = 0;
+        is_inf[m] = 1;
+      } else {
+        affine_to_bytes(acc.to_affine(), out_bytes + m * nbytes, modbytes);
+        is_inf[m] = 0;
+      }
+    }
+  }
+}
+
 }  // namespace kzgb200
 #endif
