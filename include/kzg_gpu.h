@@ -67,7 +67,11 @@ void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
 /* Tunables (mostly for bench/tests): "window_bits" (0 = auto), "precompute" (0: none, 1: build the per-SRS
  * G1 window table T[w][i] = 2^(c*w) G_i at srs_load / setup_powers, 2: also for G2), "profile" (record
  * per-phase CUDA events, see kzg_gpu_phase_times), "task_chunk", "reduce_chunk", "setup_g2" (0: setup_powers with a NULL
- * g2_out generates a G1-only SRS).  Takes effect at the next srs_load / setup_powers / MSM. */
+ * g2_out generates a G1-only SRS), "team" (1: latency-bound reduction levels on 4-lane teams), "long_division"
+ * (many-root quotient of one polynomial: 0 systolic, 1 one CTA, 2 8-CTA cluster), "affine_levels" (batched-affine
+ * pre-reduction levels, -1 = auto = off), "finish_affine" (0: an MSM leaves only its projective result for
+ * kzg_gpu_msm_partial_device — the point-range split folds and normalises once, after the exchange).
+ * Takes effect at the next srs_load / setup_powers / MSM. */
 int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value);
 
 /* Make an SRS resident.  g1: n * 2M bytes.  g2: n * 4M bytes or NULL (G1-only use). */

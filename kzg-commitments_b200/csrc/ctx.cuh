@@ -67,7 +67,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 2;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 2, opt_finish_affine = 1;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -469,11 +469,11 @@ struct Ctx final : kzg_gpu_ctx {
     if (opt_team && sh.groups_per_msm > 1 && batch <= TEAM_MAX_ITEMS)  // Horner over the windows: a long dependent chain
       msm_finish_team<F><<<(unsigned)((4 * batch + 127) / 128), 128, 0, stream>>>(
           batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
-          out_xyzz.as<XYZZ<F>>());
+          out_xyzz.as<XYZZ<F>>(), opt_finish_affine);
     else
       msm_finish<F><<<(unsigned)((batch + 31) / 32), 32, 0, stream>>>(
           batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
-          out_xyzz.as<XYZZ<F>>());
+          out_xyzz.as<XYZZ<F>>(), opt_finish_affine);
     LAUNCHED();
     phase_mark(4);
     last_batch = batch;
@@ -576,7 +576,7 @@ struct Ctx final : kzg_gpu_ctx {
     if (!d_words || n == 0 || n > 4096) return KZG_GPU_ERR_ARG;
     CK(out_bytes.ensure(4 * M));
     CK(out_inf.ensure(sizeof(int)));
-    sum_points<Fp><<<1, 1, 0, stream>>>(n, static_cast<const XYZZ<Fp>*>(d_words), out_bytes.as<uint8_t>(), out_inf.as<int>(), M);
+    sum_points_team<Fp><<<1, 512, 0, stream>>>(n, static_cast<const XYZZ<Fp>*>(d_words), out_bytes.as<uint8_t>(), out_inf.as<int>(), M);
     LAUNCHED();
     last_batch = 1;
     last_group = 1;
@@ -590,7 +590,7 @@ struct Ctx final : kzg_gpu_ctx {
     CK(out_bytes.ensure(4 * M));
     CK(out_inf.ensure(sizeof(int)));
     CK(cudaMemcpyAsync(partial.p, words, n * sizeof(XYZZ<Fp>), cudaMemcpyHostToDevice, stream));
-    sum_points<Fp><<<1, 1, 0, stream>>>(n, partial.as<XYZZ<Fp>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M);
+    sum_points_team<Fp><<<1, 512, 0, stream>>>(n, partial.as<XYZZ<Fp>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M);
     LAUNCHED();
     last_batch = 1;
     last_group = 1;

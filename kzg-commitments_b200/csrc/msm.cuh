@@ -565,13 +565,17 @@ template <class P> struct CoordCount<Field2<P>> { static constexpr int value = 4
 // out_xyzz (optional) also receives the projective result (used by the multi-GPU partial sums).
 template <class F>
 KZG_HD void msm_finish_thread(int groups_per_msm, int c, const XYZZ<F>* group_out, uint8_t* out_bytes, int* is_inf,
-                              int modbytes, XYZZ<F>* out_xyzz, uint64_t m) {
+                              int modbytes, XYZZ<F>* out_xyzz, uint64_t m, int want_affine = 1) {
   XYZZ<F> acc = group_out[m * groups_per_msm + (groups_per_msm - 1)];
   for (int g = groups_per_msm - 2; g >= 0; g--) {
     for (int k = 0; k < c; k++) acc.dbl();
     acc.add(group_out[m * groups_per_msm + g]);
   }
   if (out_xyzz) out_xyzz[m] = acc;
+  if (!want_affine) {  // the caller only wants the projective partial (point-range split across GPUs)
+    is_inf[m] = acc.is_inf() ? 1 : 0;
+    return;
+  }
   const int nbytes = CoordCount<F>::value * modbytes;
   if (acc.is_inf()) {
     for (int j = 0; j < nbytes; j++) out_bytes[m * nbytes + j] = 0;
@@ -585,10 +589,10 @@ KZG_HD void msm_finish_thread(int groups_per_msm, int c, const XYZZ<F>* group_ou
 template <class F>
 __global__ void msm_finish(uint64_t batch, int groups_per_msm, int c, const XYZZ<F>* __restrict__ group_out,
                            uint8_t* __restrict__ out_bytes, int* __restrict__ is_inf, int modbytes,
-                           XYZZ<F>* __restrict__ out_xyzz) {
+                           XYZZ<F>* __restrict__ out_xyzz, int want_affine) {
   const uint64_t m = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
   if (m >= batch) return;
-  msm_finish_thread<F>(groups_per_msm, c, group_out, out_bytes, is_inf, modbytes, out_xyzz, m);
+  msm_finish_thread<F>(groups_per_msm, c, group_out, out_bytes, is_inf, modbytes, out_xyzz, m, want_affine);
 }
 
 // out = sum of n projective points (the fold of the per-GPU partial sums of a point-range split)

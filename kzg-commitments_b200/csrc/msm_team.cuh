@@ -208,7 +208,8 @@ msm_group_combine_team(uint64_t groups, int h, const XYZZ<F>* __restrict__ t1, c
 template <class F>
 __global__ void __launch_bounds__(128)
 msm_finish_team(uint64_t batch, int groups_per_msm, int c, const XYZZ<F>* __restrict__ group_out,
-                uint8_t* __restrict__ out_bytes, int* __restrict__ is_inf, int modbytes, XYZZ<F>* __restrict__ out_xyzz) {
+                uint8_t* __restrict__ out_bytes, int* __restrict__ is_inf, int modbytes, XYZZ<F>* __restrict__ out_xyzz,
+                int want_affine) {
   KZG_TEAM_LOOP(m, batch) {
     XYZZ<F> acc = group_out[m * groups_per_msm + (groups_per_msm - 1)];
     for (int g = groups_per_msm - 2; g >= 0; g--) {
@@ -219,13 +220,53 @@ msm_finish_team(uint64_t batch, int groups_per_msm, int c, const XYZZ<F>* __rest
     if ((threadIdx.x & 3) == 0) {
       if (out_xyzz) out_xyzz[m] = acc;
       const int nbytes = CoordCount<F>::value * modbytes;
-      if (acc.is_inf()) {
+      if (!want_affine) {
+        is_inf[m] = acc.is_inf() ? 1 : 0;
+      } else if (acc.is_inf()) {
         for (int j = 0; j < nbytes; j++) out_bytes[m * nbytes + j] = 0;
         is_inf[m] = 1;
       } else {
         affine_to_bytes(acc.to_affine(), out_bytes + m * nbytes, modbytes);
         is_inf[m] = 0;
       }
+    }
+  }
+}
+
+// sum of n projective points (the partial sums of a point-range split gathered from all ranks), then affine bytes:
+// 128 teams take strided slices, a shared-memory tree joins them (log2 levels of one team addition each).
+template <class F>
+__global__ void __launch_bounds__(512)
+sum_points_team(uint64_t n, const XYZZ<F>* __restrict__ pts, uint8_t* __restrict__ out_bytes, int* __restrict__ is_inf,
+                int modbytes) {
+  __shared__ XYZZ<F> sh[128];
+  const int team = threadIdx.x >> 2;
+  const unsigned mask = Team().mask;
+  XYZZ<F> acc = XYZZ<F>::inf();
+  for (uint64_t i = team; i < n; i += 128) {
+    const XYZZ<F> v = pts[i];
+    acc = team_add<F>(acc, v);
+  }
+  if ((threadIdx.x & 3) == 0) sh[team] = acc;
+  __syncthreads();
+  for (int stride = 64; stride >= 1; stride >>= 1) {
+    if (team < stride) {
+      const XYZZ<F> a = sh[team], b = sh[team + stride];
+      const XYZZ<F> s = team_add<F>(a, b);
+      __syncwarp(mask);
+      if ((threadIdx.x & 3) == 0) sh[team] = s;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const XYZZ<F> total = sh[0];
+    const int nbytes = CoordCount<F>::value * modbytes;
+    if (total.is_inf()) {
+      for (int j = 0; j < nbytes; j++) out_bytes[j] = 0;
+      is_inf[0] = 1;
+    } else {
+      affine_to_bytes(total.to_affine(), out_bytes, modbytes);
+      is_inf[0] = 0;
     }
   }
 }

@@ -260,6 +260,23 @@ def test_batch_and_point_range_split(ctxs):
     torch.cuda.synchronize()
     xy, inf = ctx.g1_sum_partials_device(allp, 4)
     assert xy == full and not inf
+    # ranks of a point-range split skip their own affine normalisation (finish_affine = 0): the projective partial is
+    # the same group element (its representation depends on the order the atomics sorted the records in); and a
+    # fold of many partials (more than the 128 teams of the fold kernel hold at once, infinity included)
+    ctx.set_option("finish_affine", 0)
+    ctx.msm_g1(C.scalars_to_bytes(blobs[0][:n // 4]), n // 4, base_offset=0)
+    first = ctx.msm_fetch_partial()
+    ctx.set_option("finish_affine", 1)
+    xy, inf = ctx.g1_sum_partials([first] + partials[1:])
+    assert xy == full and not inf
+    many = []
+    for g in range(150):
+        lo, hi = g * n // 150, (g + 1) * n // 150
+        ctx.msm_g1(C.scalars_to_bytes(blobs[0][lo:hi]), hi - lo, base_offset=lo)
+        many.append(ctx.msm_fetch_partial())
+    many.insert(7, bytes(len(many[0])))  # the point at infinity (ZZ = 0)
+    xy, inf = ctx.g1_sum_partials(many)
+    assert xy == full and not inf
 
 
 def test_msm_2_16_linearity_and_oracle(ctxs):
