@@ -16,10 +16,12 @@ sys.path.insert(0, os.path.join(ROOT, "kzg-commitments_b200"))
 import kzg_b200  # noqa: E402
 
 
-def random_scalars(n, seed, top=0x73eda753299d7d48):
+def random_scalars(n, seed, r=0x73eda753299d7d483339d80809a1d80553bda402fffe5bfeffffffff00000001, sb=32):
+    """n uniform scalars below (top 64 bits of r) << (8*sb - 64), i.e. below r, as an (n, sb) uint8 array (little-endian)."""
     rng = np.random.default_rng(seed)
-    a = rng.integers(0, 1 << 63, size=(n, 4), dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=(n, 4), dtype=np.uint64)
-    a[:, 3] = rng.integers(0, top, size=n, dtype=np.uint64)
+    a = rng.integers(0, 256, size=(n, sb), dtype=np.uint8)
+    top = rng.integers(0, r >> (8 * (sb - 8)), size=n, dtype=np.uint64)
+    a[:, sb - 8:] = top.view(np.uint8).reshape(n, 8)
     return a
 
 
@@ -44,7 +46,7 @@ def main():
     ctx.set_option("profile", 1)
     for lg in [int(x) for x in args.sizes.split(",")]:
         n = 1 << lg
-        sc = torch.from_numpy(random_scalars(n, lg).view(np.uint8).reshape(-1)).cuda()
+        sc = torch.from_numpy(random_scalars(n, lg, ctx.r, ctx.SB).reshape(-1)).cuda()
         for pre in [int(x) for x in args.precompute.split(",")]:
             for wb in [int(x) for x in args.windows.split(",")]:
                 ctx.set_option("precompute", pre)
