@@ -68,7 +68,8 @@ void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
  * G1 window table T[w][i] = 2^(c*w) G_i at srs_load / setup_powers, 2: also for G2), "profile" (record
  * per-phase CUDA events, see kzg_gpu_phase_times), "task_chunk", "reduce_chunk", "setup_g2" (0: setup_powers with a NULL
  * g2_out generates a G1-only SRS), "team" (1: latency-bound reduction levels on 4-lane teams), "long_division"
- * (many-root quotient of one polynomial: 0 systolic, 1 one CTA, 2 8-CTA cluster), "affine_levels" (batched-affine
+ * (many-root quotient of one polynomial: 0 systolic, 1 long division on one CTA, 2 on an 8-CTA cluster,
+ * 3 = default: power-series inversion with truncated products over the whole GPU), "affine_levels" (batched-affine
  * pre-reduction levels, -1 = auto = off), "finish_affine" (0: an MSM leaves only its projective result for
  * kzg_gpu_msm_partial_device — the point-range split folds and normalises once, after the exchange).
  * Takes effect at the next srs_load / setup_powers / MSM. */

@@ -64,7 +64,7 @@ int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value) {
   if (n == "window_bits") { if (value != 0 && (value < 2 || value > 22)) return KZG_GPU_ERR_ARG; ctx->opt_window_bits = (int)value; }
   else if (n == "precompute") { if (value < 0 || value > 2) return KZG_GPU_ERR_ARG; ctx->opt_precompute = (int)value; }
   else if (n == "profile") ctx->opt_profile = value ? 1 : 0;
-  else if (n == "long_division") { if (value < 0 || value > 2) return KZG_GPU_ERR_ARG; ctx->opt_long_division = (int)value; }
+  else if (n == "long_division") { if (value < 0 || value > 3) return KZG_GPU_ERR_ARG; ctx->opt_long_division = (int)value; }
   else if (n == "finish_affine") ctx->opt_finish_affine = value ? 1 : 0;
   else if (n == "team") { if (value < 0 || value > 1) return KZG_GPU_ERR_ARG; ctx->opt_team = (int)value; }
   else if (n == "affine_levels") { if (value < -1 || value > 4) return KZG_GPU_ERR_ARG; ctx->opt_affine_levels = (int)value; }

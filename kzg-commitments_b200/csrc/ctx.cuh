@@ -67,7 +67,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 2, opt_finish_affine = 1;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -132,7 +132,7 @@ struct Ctx final : kzg_gpu_ctx {
   DevBuf fb1, fb2;
   bool fb_ready = false;
   // scratch
-  DevBuf raw, stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
+  DevBuf nt_g0, nt_g1, nt_u, raw, stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
       out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3, aff_off, aff_a, aff_b, aff_prefix,
       aff_totals, roots, inv_fact, it_u, it_pa, it_pb, it_za, it_zb;
   uint64_t inv_fact_n = 0;
@@ -142,7 +142,7 @@ struct Ctx final : kzg_gpu_ctx {
 
   ~Ctx() override {
     cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &raw, &stage, &scal, &digits, &counts, &starts, &task_first,
+    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
                       &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
@@ -630,12 +630,40 @@ struct Ctx final : kzg_gpu_ctx {
   // d_roots: device array of the first roots (batched form) or nullptr (single polynomial, first_root).
   int enqueue_quotient(uint64_t n, int64_t first_root, uint64_t k, uint64_t batch = 1, const long long* d_roots = nullptr) {
     const Fr* q;
-    if (k < 48) {  // a few opened points: one CTA-wide suffix scan per root
+    // measured on B200 at degree 4095 (tools/gpu_probe_quotient.py): the scan kernel costs 0.08 ms per root, the
+    // power-series path 0.69 ms whatever k is -> series from 8 roots on
+    const bool series = batch == 1 && !d_roots && opt_long_division >= 3 && k >= 8 && k <= 16384 && n - k <= 16384;
+    if (k < 48 && !series) {  // a few opened points: one CTA-wide suffix scan per root
       constexpr int QT = 512;
       poly_quotient_rounds<C, QT><<<(unsigned)batch, QT, 0, stream>>>(n, (long long)first_root, d_roots, k, poly0.as<Fr>(),
                                                                       poly1.as<Fr>());
       LAUNCHED();
       q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
+    } else if (series) {
+      // one polynomial, many roots: rev(q) = rev(P) * rev(Z)^-1 mod x^L, all truncated products over the whole GPU
+      Fr *pz = nullptr, *zz = nullptr;
+      int rc = enqueue_interpolate(first_root, k, &pz, &zz, false);  // Z (k + 1 coefficients, monic)
+      if (rc) return rc;
+      const uint64_t L = n - k;
+      for (DevBuf* bf : {&nt_g0, &nt_g1, &nt_u}) CK(bf->ensure(L * sizeof(Fr)));
+      Fr *g = nt_g0.as<Fr>(), *g2 = nt_g1.as<Fr>(), *u = nt_u.as<Fr>();
+      auto grid_for = [](uint64_t outs) { return (unsigned)std::min<uint64_t>((outs + 3) / 4, 148 * 32); };
+      // g = 1 / rev(Z) mod x^1 = 1 (Z is monic); f = rev(Z) is read in place: f[t] = Z[k - t], only its first
+      // min(k + 1, 2m) coefficients matter at precision 2m
+      poly_mul_trunc<C><<<1, 128, 0, stream>>>(zz, 1, (long long)k, zz, 1, (long long)k, g, 1, 0, 0);  // 1 * 1
+      LAUNCHED();
+      for (uint64_t m = 1; m < L; m <<= 1) {
+        const uint64_t m2 = std::min<uint64_t>(2 * m, L), nf = std::min<uint64_t>(k + 1, m2);
+        poly_mul_trunc<C><<<grid_for(m2), 128, 0, stream>>>(zz, nf, (long long)k, g, m, -1, u, m2, 1, 0);   // u = 2 - f g
+        LAUNCHED();
+        poly_mul_trunc<C><<<grid_for(m2), 128, 0, stream>>>(g, m, -1, u, m2, -1, g2, m2, 0, 0);              // g' = g u
+        LAUNCHED();
+        std::swap(g, g2);
+      }
+      // rev(q) = rev(P)[0..L) * g mod x^L, written back to front: q[i] = rev(q)[L - 1 - i]
+      poly_mul_trunc<C><<<grid_for(L), 128, 0, stream>>>(poly0.as<Fr>(), L, (long long)(n - 1), g, L, -1, poly1.as<Fr>(), L, 0, 1);
+      LAUNCHED();
+      q = poly1.as<Fr>();
     } else if (batch == 1 && !d_roots && k <= 4096 && opt_long_division) {
       // one polynomial, many roots: Z from the product tree (no P part), then CTA-wide long division
       Fr *pz = nullptr, *zz = nullptr;

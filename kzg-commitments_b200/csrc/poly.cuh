@@ -448,4 +448,39 @@ poly_long_division_cluster(uint64_t n, uint32_t k, const Field<typename C::FrP>*
   cluster.sync();  // no CTA exits while a peer may still write into its shared memory
 }
 
+// ---- quotient by power-series inversion (one polynomial, many roots): q = P div Z with deg Z = k, L = n - k:
+//   rev(q) = rev(P) * rev(Z)^-1  mod x^L,   rev(Z)^-1 by Newton doubling  g <- g (2 - f g) mod x^(2m).
+// Every step is a truncated schoolbook product, a warp per output coefficient: ~3.2 L^2 modmuls in all, spread
+// over the whole GPU in ~3 log2 L launches, instead of L dependent steps on one CTA / one cluster.
+// out[i] = sum_t a[t] b[i - t] (i < nout);  two_minus: out = 2 [i == 0] - that.  With a_rev / b_rev the operand
+// is read back to front (a[t] := a_base[a_last - t]), which is how rev(P) and rev(Z) are consumed in place, and
+// out_rev writes the result back to front (out[nout - 1 - i]).
+template <class C>
+__global__ void __launch_bounds__(128)
+poly_mul_trunc(const Field<typename C::FrP>* __restrict__ a, uint64_t na, long long a_last,
+               const Field<typename C::FrP>* __restrict__ b, uint64_t nb, long long b_last,
+               Field<typename C::FrP>* __restrict__ out, uint64_t nout, int two_minus, int out_rev) {
+  using Fr = Field<typename C::FrP>;
+  const int lane = threadIdx.x & 31;
+  const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t i = warp; i < nout; i += nwarps) {
+    const uint64_t t_lo = i >= nb ? i - nb + 1 : 0, t_hi = i < na ? i : na - 1;
+    Fr acc = Fr::zero();
+    for (uint64_t t = t_lo + lane; t <= t_hi; t += 32) {
+      const Fr x = a_last >= 0 ? a[a_last - (long long)t] : a[t];
+      const Fr y = b_last >= 0 ? b[b_last - (long long)(i - t)] : b[i - t];
+      acc = Fr::add(acc, Fr::mul(x, y));
+    }
+    acc = warp_sum_field<Fr>(acc);
+    if (lane == 0) {
+      if (two_minus) {
+        acc = Fr::neg(acc);
+        if (i == 0) acc = Fr::add(acc, Fr::dbl(Fr::one()));
+      }
+      out[out_rev ? nout - 1 - i : i] = acc;
+    }
+  }
+}
+
 }  // namespace kzgb200

@@ -325,16 +325,16 @@ def test_quotient_many_roots_systolic(ctxs, cname):
     n = 1501
     coeffs = [rng.randrange(C.r) for _ in range(n)]
     raw = C.scalars_to_bytes(coeffs)
-    for long_division in (2, 1, 0):
+    for long_division in (3, 2, 1, 0):
         ctx.set_option("long_division", long_division)
-        for off, k in ((0, 47), (0, 48), (3, 64), (10, 512), (1, 700), (5, 1300), (0, 1500)):
+        for off, k in ((2, 7), (4, 8), (0, 47), (0, 48), (3, 64), (10, 512), (1, 700), (5, 1300), (0, 1500)):
             q, _, _ = C.poly_quotient(coeffs, off, k)
             assert ctx.poly_quotient(raw, off, k) == C.scalars_to_bytes(q), (long_division, off, k)
     n2 = 2600  # 2 and 4 window elements per thread (k > 1024, k > 2048), window not a multiple of the CTA size
     coeffs2 = [rng.randrange(C.r) for _ in range(n2)]
     for off, k in ((2, 1025), (0, 2048), (7, 2100)):
         q, _, _ = C.poly_quotient(coeffs2, off, k)
-        for long_division in (1, 2):
+        for long_division in (1, 2, 3):
             ctx.set_option("long_division", long_division)
             assert ctx.poly_quotient(C.scalars_to_bytes(coeffs2), off, k) == C.scalars_to_bytes(q), (long_division, off, k)
     # proof through the chained path equals [q(s)]G

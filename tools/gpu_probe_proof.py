@@ -14,7 +14,7 @@ ctx.setup_powers(123456789, 5000, want_bytes=False)
 rng = random.Random(1)
 n = 4096
 raw = b"".join(rng.randrange(ctx.r).to_bytes(ctx.SB, "little") for _ in range(n))
-for mode in (2,):
+for mode in (3, 2):
     ctx.set_option("long_division", mode)
     for k in (128, 256, 512, 1024, 2048):
         ctx.prove(raw, 0, k)
