@@ -487,9 +487,12 @@ struct Ctx final : kzg_gpu_ctx {
           batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
           out_xyzz.as<XYZZ<F>>(), opt_finish_affine);
     else
-      msm_finish<F><<<(unsigned)((batch + 31) / 32), 32, 0, stream>>>(
+    {
+      const int lane_stride = batch <= 65536 ? 32 : 1;
+      msm_finish<F><<<(unsigned)((batch * lane_stride + 127) / 128), 128, 0, stream>>>(
           batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
-          out_xyzz.as<XYZZ<F>>(), opt_finish_affine);
+          out_xyzz.as<XYZZ<F>>(), opt_finish_affine, lane_stride);
+    }
     LAUNCHED();
     phase_mark(4);
     last_batch = batch;
