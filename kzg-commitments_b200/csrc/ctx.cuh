@@ -61,7 +61,8 @@ int ilog2(uint64_t v) {
 struct kzg_gpu_ctx {
   int curve = -1;
   int device = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr, copy_stream = nullptr;
+  cudaEvent_t copied_ev[2] = {nullptr, nullptr}, consumed_ev[2] = {nullptr, nullptr};
   std::string last_error;
   uint64_t launches = 0;
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
@@ -132,7 +133,7 @@ struct Ctx final : kzg_gpu_ctx {
   DevBuf fb1, fb2;
   bool fb_ready = false;
   // scratch
-  DevBuf nt_g0, nt_g1, nt_u, raw, stage, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
+  DevBuf nt_g0, nt_g1, nt_u, raw, stage, scal2, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
       out_inf, out_xyzz, poly0, poly1, qbytes, powers, tile_sums, hist, tasks, slot_seg, ranks, red0, red1, red2, red3, aff_off, aff_a, aff_b, aff_prefix,
       aff_totals, roots, inv_fact, it_u, it_pa, it_pb, it_za, it_zb;
   uint64_t inv_fact_n = 0;
@@ -142,11 +143,16 @@ struct Ctx final : kzg_gpu_ctx {
 
   ~Ctx() override {
     cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal, &digits, &counts, &starts, &task_first,
+    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
                       &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
     for (cudaEvent_t e : phase_ev) if (e) cudaEventDestroy(e);
+    for (int i = 0; i < 2; i++) {
+      if (copied_ev[i]) cudaEventDestroy(copied_ev[i]);
+      if (consumed_ev[i]) cudaEventDestroy(consumed_ev[i]);
+    }
+    if (copy_stream) cudaStreamDestroy(copy_stream);
     if (stream) cudaStreamDestroy(stream);
   }
 
@@ -527,12 +533,44 @@ struct Ctx final : kzg_gpu_ctx {
     }
     const bool use_table = group == 1 ? g1_table.p != nullptr : g2_table.p != nullptr;
     const int Wguess = use_table ? table_W : (C::SCALAR_BITS + 8) / 8;
-    const uint64_t per_pass = do_fetch ? max_batch_per_pass(count, Wguess) : batch;
-    for (uint64_t b0 = 0; b0 < batch; b0 += per_pass) {
+    uint64_t per_pass = do_fetch ? max_batch_per_pass(count, Wguess) : batch;
+    // Host scalars of a large batch: split into passes of >= 128 MSMs so that the copy of pass i + 1 (copy stream,
+    // second staging buffer) runs under the kernels of pass i; one pass would leave the whole H2D exposed
+    // (134 MB = 2.4 ms for 1024 blobs of 4096 coefficients in front of 35 ms of compute).
+    const bool pipelined = !on_device && do_fetch && batch >= 256 && count * batch * (uint64_t)SB >= (32ull << 20);
+    if (pipelined) per_pass = std::min<uint64_t>(per_pass, std::max<uint64_t>(128, (batch + 3) / 4));
+    if (pipelined && !copy_stream) {
+      CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+      for (int i = 0; i < 2; i++) {
+        CK(cudaEventCreateWithFlags(&copied_ev[i], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&consumed_ev[i], cudaEventDisableTiming));
+      }
+    }
+    DevBuf* stage_buf[2] = {&scal, &scal2};
+    auto enqueue_copy = [&](uint64_t pass, uint64_t b0) -> int {  // pass -> staging buffer pass % 2, on the copy stream
+      const uint64_t nb = std::min(per_pass, batch - b0);
+      DevBuf* sb = stage_buf[pass & 1];
+      if (pass >= 2) CK(cudaStreamWaitEvent(copy_stream, consumed_ev[pass & 1], 0));  // its previous user has finished
+      CK(sb->ensure(per_pass * count * (size_t)SB));
+      CK(cudaMemcpyAsync(sb->p, scalars + b0 * count * SB, nb * count * (size_t)SB, cudaMemcpyHostToDevice, copy_stream));
+      CK(cudaEventRecord(copied_ev[pass & 1], copy_stream));
+      return KZG_GPU_OK;
+    };
+    if (pipelined) {
+      CK(scal.ensure(per_pass * count * (size_t)SB));   // both buffers at their final size before any copy is in flight
+      CK(scal2.ensure(per_pass * count * (size_t)SB));
+      int rc = enqueue_copy(0, 0);
+      if (rc) return rc;
+    }
+    uint64_t pass = 0;
+    for (uint64_t b0 = 0; b0 < batch; b0 += per_pass, pass++) {
       const uint64_t nb = std::min(per_pass, batch - b0);
       const uint8_t* d_scal;
       if (on_device) {
         d_scal = scalars + b0 * count * SB;
+      } else if (pipelined) {
+        CK(cudaStreamWaitEvent(stream, copied_ev[pass & 1], 0));
+        d_scal = stage_buf[pass & 1]->as<uint8_t>();
       } else {
         CK(scal.ensure(nb * count * (size_t)SB));
         CK(cudaMemcpyAsync(scal.p, scalars + b0 * count * SB, nb * count * (size_t)SB, cudaMemcpyHostToDevice, stream));
@@ -546,6 +584,13 @@ struct Ctx final : kzg_gpu_ctx {
         rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), use_table ? g2_table.as<Affine<Fp2>>() : nullptr, table_c, d_scal,
                               count, nb, base_offset);
       if (rc) return rc;
+      if (pipelined) {
+        CK(cudaEventRecord(consumed_ev[pass & 1], stream));
+        if (b0 + per_pass < batch) {  // the next pass's copy goes out while this pass computes
+          rc = enqueue_copy(pass + 1, b0 + per_pass);
+          if (rc) return rc;
+        }
+      }
       if (do_fetch) {
         rc = fetch_locked(out ? out + b0 * (size_t)(nco * M) : nullptr, is_inf ? is_inf + b0 : nullptr);
         if (rc) return rc;

@@ -484,3 +484,33 @@ def test_commit_bytes_device_chain(ctxs, cname):
         ts.commit_bytes(b"x" * 10, 5, byte_offset=3)
     c0, p0 = ts.commit_bytes(b"", 4)
     assert c0.is_inf and len(p0) == 0
+
+
+def test_batch_host_scalars_pipelined_passes(ctxs):
+    """A host-scalar batch large enough for the pipelined path of kzg_gpu_msm_g1_batch (passes of >= 128 MSMs, the
+    copy of pass i + 1 under the kernels of pass i, two staging buffers): 300 blobs x 4096 coefficients in three
+    ragged passes must give the bytes of the device-resident batch and of single-MSM calls, twice in a row."""
+    import numpy as np
+    import torch
+    cname = "bls12381"
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    ctx.set_option("precompute", 2)
+    ctx.set_option("window_bits", 0)
+    n, batch = 4096, 300
+    kzg_b200.TrustedSetup.generate(cname, n + 1, 0x1234567, ctx=ctx)
+    rng = np.random.default_rng(99)
+    a = rng.integers(0, 256, size=(batch * n, 32), dtype=np.uint8)
+    a[:, 31] &= 0x3F  # below r
+    a[5 * n:6 * n] = 0  # one all-zero blob -> infinity
+    host = a.reshape(-1).tobytes()
+    dev = torch.from_numpy(a.reshape(-1)).cuda()
+    ctx.msm_g1_launch(dev, n, batch, 0)
+    want, want_inf = ctx.msm_fetch(batch)
+    for _ in range(2):
+        out, infs = ctx.msm_g1_batch(host, n, batch)
+        assert out == want and infs == want_inf
+    assert infs[5] and not infs[4]
+    for b in (0, 127, 128, 255, 256, 299):  # both sides of every pass boundary
+        xy, inf = ctx.msm_g1(host[b * n * 32:(b + 1) * n * 32], n, 0)
+        assert out[b * 96:(b + 1) * 96] == xy and not inf
