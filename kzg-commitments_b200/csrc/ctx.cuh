@@ -63,6 +63,8 @@ struct kzg_gpu_ctx {
   int device = 0;
   cudaStream_t stream = nullptr, copy_stream = nullptr;
   cudaEvent_t copied_ev[2] = {nullptr, nullptr}, consumed_ev[2] = {nullptr, nullptr};
+  cudaEvent_t chunk_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  int chunk_slices = 0;  // set by msm() right before enqueue_msm when the scalars are still arriving in chunks
   std::string last_error;
   uint64_t launches = 0;
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
@@ -152,6 +154,7 @@ struct Ctx final : kzg_gpu_ctx {
       if (copied_ev[i]) cudaEventDestroy(copied_ev[i]);
       if (consumed_ev[i]) cudaEventDestroy(consumed_ev[i]);
     }
+    for (cudaEvent_t e : chunk_ev) if (e) cudaEventDestroy(e);
     if (copy_stream) cudaStreamDestroy(copy_stream);
     if (stream) cudaStreamDestroy(stream);
   }
@@ -368,9 +371,16 @@ struct Ctx final : kzg_gpu_ctx {
     CK(cudaMemsetAsync(hist.p, 0, (MSM_MAX_CHUNK + 2) * 4, stream));
     {
       const uint64_t total = count * batch;
-      unsigned grid = (unsigned)std::min<uint64_t>((total + 255) / 256, (uint64_t)sms * 16);
-      msm_digits<C><<<grid, 256, 0, stream>>>(sh, d_scalars, digits.as<int32_t>(), ranks.as<uint32_t>(), counts.as<uint32_t>());
-      LAUNCHED();
+      const int slices = chunk_slices > 1 ? chunk_slices : 1;  // > 1: the scalars arrive in that many H2D chunks
+      for (int sl = 0; sl < slices; sl++) {
+        const uint64_t t0 = total * sl / slices, t1 = total * (sl + 1) / slices;
+        if (slices > 1) CK(cudaStreamWaitEvent(stream, chunk_ev[sl], 0));
+        unsigned grid = (unsigned)std::min<uint64_t>((t1 - t0 + 255) / 256, (uint64_t)sms * 16);
+        msm_digits<C><<<grid, 256, 0, stream>>>(sh, d_scalars, digits.as<int32_t>(), ranks.as<uint32_t>(), counts.as<uint32_t>(),
+                                                t0, t1);
+        LAUNCHED();
+      }
+      chunk_slices = 0;
     }
     int rc = enqueue_scan(nbuckets, 0, counts.as<uint32_t>(), starts.as<uint32_t>(), nullptr);
     if (rc) return rc;
@@ -566,11 +576,30 @@ struct Ctx final : kzg_gpu_ctx {
     for (uint64_t b0 = 0; b0 < batch; b0 += per_pass, pass++) {
       const uint64_t nb = std::min(per_pass, batch - b0);
       const uint8_t* d_scal;
+      chunk_slices = 0;
       if (on_device) {
         d_scal = scalars + b0 * count * SB;
       } else if (pipelined) {
         CK(cudaStreamWaitEvent(stream, copied_ev[pass & 1], 0));
         d_scal = stage_buf[pass & 1]->as<uint8_t>();
+      } else if (nb * count * (uint64_t)SB >= (8ull << 20) && nb * count >= 4 * 65536) {
+        // one large host MSM: the scalars go over in 4 chunks on the copy stream and the digit kernel starts on
+        // each chunk as it lands, so only the last quarter's digits are left after the copy (enqueue_msm, slices)
+        CK(scal.ensure(nb * count * (size_t)SB));
+        if (!copy_stream) CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+        for (int sl = 0; sl < 4; sl++)
+          if (!chunk_ev[sl]) CK(cudaEventCreateWithFlags(&chunk_ev[sl], cudaEventDisableTiming));
+        CK(cudaEventRecord(chunk_ev[0], stream));              // the staging buffer's previous readers are done
+        CK(cudaStreamWaitEvent(copy_stream, chunk_ev[0], 0));
+        const uint64_t total = nb * count;
+        for (int sl = 0; sl < 4; sl++) {
+          const uint64_t t0 = total * sl / 4, t1 = total * (sl + 1) / 4;
+          CK(cudaMemcpyAsync(scal.as<uint8_t>() + t0 * SB, scalars + (b0 * count + t0) * SB, (t1 - t0) * (size_t)SB,
+                             cudaMemcpyHostToDevice, copy_stream));
+          CK(cudaEventRecord(chunk_ev[sl], copy_stream));
+        }
+        chunk_slices = 4;
+        d_scal = scal.as<uint8_t>();
       } else {
         CK(scal.ensure(nb * count * (size_t)SB));
         CK(cudaMemcpyAsync(scal.p, scalars + b0 * count * SB, nb * count * (size_t)SB, cudaMemcpyHostToDevice, stream));

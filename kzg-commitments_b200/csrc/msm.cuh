@@ -122,9 +122,10 @@ KZG_HD void msm_digits_thread(const MsmShape& sh, const uint8_t* scalars, int32_
 #if defined(__CUDACC__)
 template <class C>
 __global__ void msm_digits(MsmShape sh, const uint8_t* __restrict__ scalars, int32_t* __restrict__ digits,
-                           uint32_t* __restrict__ ranks, uint32_t* __restrict__ counts) {
-  const uint64_t total = sh.n * sh.batch;
-  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total;
+                           uint32_t* __restrict__ ranks, uint32_t* __restrict__ counts, uint64_t t_begin,
+                           uint64_t t_end) {
+  // scalars [t_begin, t_end) of the n * batch: the host path launches one slice per arriving H2D chunk
+  for (uint64_t t = t_begin + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < t_end;
        t += (uint64_t)gridDim.x * blockDim.x)
     msm_digits_thread<C>(sh, scalars, digits, ranks, counts, t);
 }
