@@ -549,11 +549,11 @@ struct Ctx final : kzg_gpu_ctx {
     // (134 MB = 2.4 ms for 1024 blobs of 4096 coefficients in front of 35 ms of compute).
     const bool pipelined = !on_device && do_fetch && batch >= 256 && count * batch * (uint64_t)SB >= (32ull << 20);
     if (pipelined) per_pass = std::min<uint64_t>(per_pass, std::max<uint64_t>(128, (batch + 3) / 4));
-    if (pipelined && !copy_stream) {
-      CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+    if (pipelined) {
+      if (!copy_stream) CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
       for (int i = 0; i < 2; i++) {
-        CK(cudaEventCreateWithFlags(&copied_ev[i], cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&consumed_ev[i], cudaEventDisableTiming));
+        if (!copied_ev[i]) CK(cudaEventCreateWithFlags(&copied_ev[i], cudaEventDisableTiming));
+        if (!consumed_ev[i]) CK(cudaEventCreateWithFlags(&consumed_ev[i], cudaEventDisableTiming));
       }
     }
     DevBuf* stage_buf[2] = {&scal, &scal2};

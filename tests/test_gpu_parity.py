@@ -498,7 +498,8 @@ def test_batch_host_scalars_pipelined_passes(ctxs):
     ctx.set_option("precompute", 2)
     ctx.set_option("window_bits", 0)
     n, batch = 4096, 300
-    kzg_b200.TrustedSetup.generate(cname, n + 1, 0x1234567, ctx=ctx)
+    ctx.set_option("setup_g2", 0)
+    ctx.setup_powers(0x1234567, n + 1, want_bytes=False)
     rng = np.random.default_rng(99)
     a = rng.integers(0, 256, size=(batch * n, 32), dtype=np.uint8)
     a[:, 31] &= 0x3F  # below r
@@ -507,6 +508,15 @@ def test_batch_host_scalars_pipelined_passes(ctxs):
     dev = torch.from_numpy(a.reshape(-1)).cuda()
     ctx.msm_g1_launch(dev, n, batch, 0)
     want, want_inf = ctx.msm_fetch(batch)
+    # one large host MSM first (its chunked copy creates the copy stream), then the pipelined batch on the same context
+    big = host[:70 * n * 32]
+    ctx.setup_powers(0x1234567, 70 * n, want_bytes=False)
+    xy_host, _ = ctx.msm_g1(big, 70 * n, 0)
+    ctx.msm_g1_launch(dev, 70 * n, 1, 0)
+    xy_dev, _ = ctx.msm_fetch(1)
+    assert xy_host == xy_dev
+    ctx.setup_powers(0x1234567, n + 1, want_bytes=False)
+    ctx.set_option("setup_g2", 1)
     for _ in range(2):
         out, infs = ctx.msm_g1_batch(host, n, batch)
         assert out == want and infs == want_inf
