@@ -428,7 +428,8 @@ def main():
     ap.add_argument("--log2n", type=int, default=20)
     ap.add_argument("--window-bits", type=int, default=0)
     ap.add_argument("--precompute", type=int, default=1)
-    ap.add_argument("--blobs", type=int, default=1024, help="blobs per GPU for the batched-commit line (0 = skip)")
+    ap.add_argument("--blobs", type=int, default=4096,
+                    help="blobs per GPU for the batched-commit line (0 = skip); 4096 at N=1 is BASELINE config 3 as named")
     ap.add_argument("--ref-sample", type=int, default=16384, help="terms per reference process per step")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
