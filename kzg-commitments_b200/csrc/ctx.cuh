@@ -132,7 +132,7 @@ struct Ctx final : kzg_gpu_ctx {
   DevBuf g1_table, g2_table; // per-SRS window tables T[w][i] = 2^(c*w) * G_i (row 0 = the SRS itself)
   int table_c = 0, table_W = 0;
   // fixed-base tables of the generators
-  DevBuf fb1, fb2;
+  DevBuf fb1, fb2, fb_sums;
   bool fb_ready = false;
   // scratch
   DevBuf nt_g0, nt_g1, nt_u, raw, stage, scal2, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
@@ -145,7 +145,7 @@ struct Ctx final : kzg_gpu_ctx {
 
   ~Ctx() override {
     cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
+    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &fb_sums, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
                       &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
@@ -1007,20 +1007,27 @@ struct Ctx final : kzg_gpu_ctx {
     setup_powers_kernel<C><<<(unsigned)((nthreads + 63) / 64), 64, 0, stream>>>(n, scal.as<uint8_t>(), per_thread, powers.as<uint32_t>());
     LAUNCHED();
     const unsigned grid = (unsigned)((n + 127) / 128);
-    fixed_base_mul<C, Fp><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb1.as<Affine<Fp>>(), g1.as<Affine<Fp>>(),
-                                                    g1_out ? stage.as<uint8_t>() : nullptr, M);
+    const unsigned grid_aff = (unsigned)(((n + FB_BATCH - 1) / FB_BATCH + 127) / 128);
+    const bool want_g2 = g2_out || opt_setup_g2;  // "setup_g2" = 0: G1-only SRS (large synthetic MSM benches)
+    CK(fb_sums.ensure(n * (want_g2 ? sizeof(XYZZ<Fp2>) : sizeof(XYZZ<Fp>))));
+    fixed_base_mul<C, Fp><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb1.as<Affine<Fp>>(), fb_sums.as<XYZZ<Fp>>());
+    LAUNCHED();
+    fixed_base_to_affine<Fp><<<grid_aff, 128, 0, stream>>>(n, fb_sums.as<XYZZ<Fp>>(), g1.as<Affine<Fp>>(),
+                                                           g1_out ? stage.as<uint8_t>() : nullptr, M);
     LAUNCHED();
     if (g1_out) CK(cudaMemcpyAsync(g1_out, stage.p, n * (size_t)(2 * M), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
-    const bool want_g2 = g2_out || opt_setup_g2;  // "setup_g2" = 0: G1-only SRS (large synthetic MSM benches)
     if (want_g2) {
       CK(g2.ensure(n * sizeof(Affine<Fp2>)));
-      fixed_base_mul<C, Fp2><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb2.as<Affine<Fp2>>(), g2.as<Affine<Fp2>>(),
-                                                       g2_out ? stage.as<uint8_t>() : nullptr, M);
+      fixed_base_mul<C, Fp2><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb2.as<Affine<Fp2>>(), fb_sums.as<XYZZ<Fp2>>());
+      LAUNCHED();
+      fixed_base_to_affine<Fp2><<<grid_aff, 128, 0, stream>>>(n, fb_sums.as<XYZZ<Fp2>>(), g2.as<Affine<Fp2>>(),
+                                                              g2_out ? stage.as<uint8_t>() : nullptr, M);
       LAUNCHED();
       if (g2_out) CK(cudaMemcpyAsync(g2_out, stage.p, n * (size_t)(4 * M), cudaMemcpyDeviceToHost, stream));
       CK(cudaStreamSynchronize(stream));
     }
+    if (fb_sums.cap > ((size_t)64 << 20)) fb_sums.release();  // 192 / 384 B per index: not kept next to a large SRS
     srs_n = n;
     have_g2 = want_g2;
     return build_table();

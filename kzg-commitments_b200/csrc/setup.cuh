@@ -65,11 +65,13 @@ __global__ void fixed_base_table(Affine<F> gen, Affine<F>* __restrict__ table) {
   table[t] = r.to_affine();
 }
 
-// out[i] = powers[i] * G  as affine bytes (reference octet body layout) and Montgomery affine points
+// sums[i] = powers[i] * G in XYZZ coordinates (normalised afterwards by fixed_base_to_affine: a per-thread
+// inversion here is a divergent binary-GCD loop that costs a warp about as much as its 33 mixed additions,
+// profiles/r1o_setup.md)
 template <class C, class F>
 __global__ void __launch_bounds__(128)
 fixed_base_mul(uint64_t n, const uint32_t* __restrict__ powers, const Affine<F>* __restrict__ table,
-               Affine<F>* __restrict__ out_points, uint8_t* __restrict__ out_bytes, int modbytes) {
+               XYZZ<F>* __restrict__ sums) {
   using Fr = Field<typename C::FrP>;
   constexpr int W = fb_windows<C>();
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
@@ -90,12 +92,45 @@ fixed_base_mul(uint64_t n, const uint32_t* __restrict__ powers, const Affine<F>*
       acc.madd(p, d < 0);
     }
   }
-  const Affine<F> a = acc.to_affine();
-  if (out_points) out_points[i] = a;
-  if (out_bytes) {
-    const int nbytes = CoordCount<F>::value * modbytes;
-    if (acc.is_inf()) { for (int j = 0; j < nbytes; j++) out_bytes[i * nbytes + j] = 0; }
-    else affine_to_bytes(a, out_bytes + i * nbytes, modbytes);
+  sums[i] = acc;
+}
+
+// out[i] = sums[i] as Montgomery affine points and as affine bytes (reference octet body layout).
+// Thread t normalises the FB_BATCH consecutive sums [t*FB_BATCH, ..) with ONE inversion (Montgomery's trick over
+// the ZZZ coordinates: 3 extra products per point); infinity (ZZ = 0) is skipped and written as (0, 0).
+constexpr int FB_BATCH = 8;
+template <class F>
+__global__ void __launch_bounds__(128)
+fixed_base_to_affine(uint64_t n, const XYZZ<F>* __restrict__ sums, Affine<F>* __restrict__ out_points,
+                     uint8_t* __restrict__ out_bytes, int modbytes) {
+  const uint64_t lo = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) * FB_BATCH;
+  if (lo >= n) return;
+  const int cnt = (int)min((uint64_t)FB_BATCH, n - lo);
+  const int nbytes = CoordCount<F>::value * modbytes;
+  F pref[FB_BATCH];  // pref[j] = prod_{v<=j} ZZZ_v over the finite sums
+  F run = F::one();
+  for (int j = 0; j < cnt; j++) {
+    const F zzz = sums[lo + j].ZZZ;
+    if (!sums[lo + j].ZZ.is_zero()) run = F::mul(run, zzz);
+    pref[j] = run;
+  }
+  F inv = F::inv(run);
+  for (int j = cnt - 1; j >= 0; j--) {
+    const XYZZ<F> p = sums[lo + j];
+    Affine<F> a = Affine<F>::inf();
+    if (!p.is_inf()) {
+      const F i3 = j > 0 ? F::mul(inv, pref[j - 1]) : inv;  // 1 / ZZZ_j
+      inv = F::mul(inv, p.ZZZ);
+      const F i1 = F::mul(p.ZZ, i3);             // 1 / Z
+      const F i2 = F::sqr(i1);                   // 1 / ZZ
+      a = Affine<F>{F::mul(p.X, i2), F::mul(p.Y, i3)};
+    }
+    if (out_points) out_points[lo + j] = a;
+    if (out_bytes) {
+      uint8_t* dst = out_bytes + (lo + j) * (uint64_t)nbytes;
+      if (p.is_inf()) { for (int b = 0; b < nbytes; b++) dst[b] = 0; }
+      else affine_to_bytes(a, dst, modbytes);
+    }
   }
 }
 

@@ -131,3 +131,42 @@ def test_blob_batch_4096_x_4096(ctx):
     # and the summed polynomial committed on the device
     xy, _ = ctx.msm_g1(C.scalars_to_bytes(summed), n)
     assert xy == C.g1_to_octet(total)[1:]
+
+
+def test_concurrent_callers_on_one_context(ctx):
+    """SURVEY 8(b) threading: create_commit / create_proof only read the SRS and may be called from several threads
+    (reference src/kzg.h:182-290 has no locks); the context serialises the shared scratch internally.  Four threads
+    issue commitments, proofs and quotients of different sizes on ONE context at once (ctypes drops the GIL for the
+    duration of each call): every result must equal the one computed alone."""
+    import threading
+    C = get_curve(CNAME)
+    s = SECRET % C.r
+    ctx.set_option("setup_g2", 0)
+    ctx.setup_powers(s, 5000, want_bytes=False)
+    jobs = []
+    for t in range(4):
+        n = (4097, 1500, 300, 4999)[t]
+        rec = _random_records(n, 50 + t)
+        jobs.append((n, rec, rec.tobytes()))
+    alone = [(ctx.msm_g1(rec, n), ctx.prove(raw, 3 + i, 2), ctx.poly_quotient(raw, 1, 5))
+             for i, (n, rec, raw) in enumerate(jobs)]
+    assert alone[0][0][0] == _xy(C, _eval(C, _ints(jobs[0][1]), s))
+    errors = []
+
+    def worker(i):
+        n, rec, raw = jobs[i]
+        try:
+            for _ in range(25):
+                got = (ctx.msm_g1(rec, n), ctx.prove(raw, 3 + i, 2), ctx.poly_quotient(raw, 1, 5))
+                if got != alone[i]:
+                    errors.append((i, "mismatch"))
+                    return
+        except Exception as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
