@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <new>
 #include <string>
@@ -132,7 +133,13 @@ struct Ctx final : kzg_gpu_ctx {
   DevBuf g1_table, g2_table; // per-SRS window tables T[w][i] = 2^(c*w) * G_i (row 0 = the SRS itself)
   int table_c = 0, table_W = 0;
   // fixed-base tables of the generators
-  DevBuf fb1, fb2, fb_sums;
+  // (constants of the curve: built once per process and device, shared by every context, never freed)
+  struct FbShared { Affine<Fp>* t1 = nullptr; Affine<Fp2>* t2 = nullptr; };
+  static std::mutex& fb_mutex() { static std::mutex m; return m; }
+  static std::map<int, FbShared>& fb_cache() { static std::map<int, FbShared> c; return c; }
+  Affine<Fp>* fb1 = nullptr;
+  Affine<Fp2>* fb2 = nullptr;
+  DevBuf fb_sums;
   bool fb_ready = false;
   // scratch
   DevBuf nt_g0, nt_g1, nt_u, raw, stage, scal2, scal, digits, counts, starts, task_first, cursor, sorted, partial, group_out, out_bytes,
@@ -145,7 +152,7 @@ struct Ctx final : kzg_gpu_ctx {
 
   ~Ctx() override {
     cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb1, &fb2, &fb_sums, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
+    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb_sums, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
                       &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
@@ -971,22 +978,35 @@ struct Ctx final : kzg_gpu_ctx {
   // ------------------------------------------------------------------ trusted setup
   int ensure_fixed_base_tables() {
     if (fb_ready) return KZG_GPU_OK;
-    constexpr int W = fb_windows<C>();
-    CK(fb1.ensure((size_t)W * FB_HALF * sizeof(Affine<Fp>)));
-    CK(fb2.ensure((size_t)W * FB_HALF * sizeof(Affine<Fp2>)));
-    Affine<Fp> gen1;
-    Affine<Fp2> gen2;
-    for (int i = 0; i < Fp::L; i++) {
-      gen1.x.v[i] = C::g1x(i); gen1.y.v[i] = C::g1y(i);
-      gen2.x.a.v[i] = C::g2xa(i); gen2.x.b.v[i] = C::g2xb(i);
-      gen2.y.a.v[i] = C::g2ya(i); gen2.y.b.v[i] = C::g2yb(i);
+    std::lock_guard<std::mutex> guard(fb_mutex());
+    FbShared& sh = fb_cache()[device];
+    if (!sh.t2) {
+      constexpr int W = fb_windows<C>();
+      Affine<Fp>* t1 = nullptr;
+      Affine<Fp2>* t2 = nullptr;
+      CK(cudaMalloc(&t1, (size_t)W * FB_HALF * sizeof(Affine<Fp>)));
+      cudaError_t e = cudaMalloc(&t2, (size_t)W * FB_HALF * sizeof(Affine<Fp2>));
+      if (e != cudaSuccess) { cudaFree(t1); CK(e); }
+      Affine<Fp> gen1;
+      Affine<Fp2> gen2;
+      for (int i = 0; i < Fp::L; i++) {
+        gen1.x.v[i] = C::g1x(i); gen1.y.v[i] = C::g1y(i);
+        gen2.x.a.v[i] = C::g2xa(i); gen2.x.b.v[i] = C::g2xb(i);
+        gen2.y.a.v[i] = C::g2ya(i); gen2.y.b.v[i] = C::g2yb(i);
+      }
+      const unsigned grid = (W * FB_HALF + 63) / 64;
+      fixed_base_table<C, Fp><<<grid, 64, 0, stream>>>(gen1, t1);
+      LAUNCHED();
+      fixed_base_table<C, Fp2><<<grid, 64, 0, stream>>>(gen2, t2);
+      LAUNCHED();
+      e = cudaStreamSynchronize(stream);
+      if (e == cudaSuccess) e = cudaGetLastError();
+      if (e != cudaSuccess) { cudaFree(t1); cudaFree(t2); CK(e); }
+      sh.t1 = t1;
+      sh.t2 = t2;
     }
-    const unsigned grid = (W * FB_HALF + 63) / 64;
-    fixed_base_table<C, Fp><<<grid, 64, 0, stream>>>(gen1, fb1.as<Affine<Fp>>());
-    LAUNCHED();
-    fixed_base_table<C, Fp2><<<grid, 64, 0, stream>>>(gen2, fb2.as<Affine<Fp2>>());
-    LAUNCHED();
-    CK(cudaStreamSynchronize(stream));
+    fb1 = sh.t1;
+    fb2 = sh.t2;
     fb_ready = true;
     return KZG_GPU_OK;
   }
@@ -1010,7 +1030,7 @@ struct Ctx final : kzg_gpu_ctx {
     const unsigned grid_aff = (unsigned)(((n + FB_BATCH - 1) / FB_BATCH + 127) / 128);
     const bool want_g2 = g2_out || opt_setup_g2;  // "setup_g2" = 0: G1-only SRS (large synthetic MSM benches)
     CK(fb_sums.ensure(n * (want_g2 ? sizeof(XYZZ<Fp2>) : sizeof(XYZZ<Fp>))));
-    fixed_base_mul<C, Fp><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb1.as<Affine<Fp>>(), fb_sums.as<XYZZ<Fp>>());
+    fixed_base_mul<C, Fp><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb1, fb_sums.as<XYZZ<Fp>>());
     LAUNCHED();
     fixed_base_to_affine<Fp><<<grid_aff, 128, 0, stream>>>(n, fb_sums.as<XYZZ<Fp>>(), g1.as<Affine<Fp>>(),
                                                            g1_out ? stage.as<uint8_t>() : nullptr, M);
@@ -1019,7 +1039,7 @@ struct Ctx final : kzg_gpu_ctx {
     CK(cudaStreamSynchronize(stream));
     if (want_g2) {
       CK(g2.ensure(n * sizeof(Affine<Fp2>)));
-      fixed_base_mul<C, Fp2><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb2.as<Affine<Fp2>>(), fb_sums.as<XYZZ<Fp2>>());
+      fixed_base_mul<C, Fp2><<<grid, 128, 0, stream>>>(n, powers.as<uint32_t>(), fb2, fb_sums.as<XYZZ<Fp2>>());
       LAUNCHED();
       fixed_base_to_affine<Fp2><<<grid_aff, 128, 0, stream>>>(n, fb_sums.as<XYZZ<Fp2>>(), g2.as<Affine<Fp2>>(),
                                                               g2_out ? stage.as<uint8_t>() : nullptr, M);
