@@ -83,6 +83,23 @@ ECP2 g2_from_body(const uint8_t* xy, int is_inf) {
   return p;
 }
 
+// G2 point from an octet body the device has just produced in kzg_gpu_setup_powers, WITHOUT the on-curve test:
+// ECP2_fromOctet -> ECP2_set -> ECP2_rhs divides the curve constant by the twist element on every call
+// (FP2_div_ip -> FP_inv, ecp2.cpp:301-318, 268-298), ~20 us per point = most of trusted_setup(4096) once the
+// scalar multiplications are on the GPU.  The result is the exact representation ECP2_set leaves (x, y, z = 1);
+// the caller still runs the checked path on a few indices, and the reference checks every point when it loads
+// an exported file.  All-zero coordinates = infinity (s = 0 only).
+ECP2 g2_from_device_body(const uint8_t* xy) {
+  ECP2 p;
+  bool zero = true;
+  for (int i = 0; i < G2_BYTES; i++) zero = zero && xy[i] == 0;
+  if (zero) { ECP2_inf(&p); return p; }
+  FP2_fromBytes(&p.x, (char*)xy);
+  FP2_fromBytes(&p.y, (char*)xy + G2_BYTES / 2);
+  FP2_one(&p.z);
+  return p;
+}
+
 // coefficients of P as flat little-endian CURVE_ORDER_BYTES records (what BIG_from_ZZ starts from, util.cpp:31-43)
 // BytesFromZZ only reads the coefficient's magnitude (no ZZ_p modulus context involved), so large polynomials are
 // packed by a few host threads: at 0.2-0.4 us per coefficient the single-threaded loop (1.2 ms for 4097
@@ -244,7 +261,8 @@ kzg::trusted_setup::trusted_setup(int num_coeff) {
   _G2.resize(n);
   for (size_t i = 0; i < n; i++) {
     _G1[i] = g1_from_body(b1.data() + i * G1_BYTES, 0);
-    _G2[i] = g2_from_body(b2.data() + i * G2_BYTES, 0);
+    const bool checked = i < 2 || i + 1 == n || i == n / 2;
+    _G2[i] = checked ? g2_from_body(b2.data() + i * G2_BYTES, 0) : g2_from_device_body(b2.data() + i * G2_BYTES);
   }
   remember(this, ctx, _G1);
 }
