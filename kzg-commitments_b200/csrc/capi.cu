@@ -66,6 +66,7 @@ int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value) {
   else if (n == "profile") ctx->opt_profile = value ? 1 : 0;
   else if (n == "long_division") { if (value < 0 || value > 3) return KZG_GPU_ERR_ARG; ctx->opt_long_division = (int)value; }
   else if (n == "finish_affine") ctx->opt_finish_affine = value ? 1 : 0;
+  else if (n == "tail") { if (value < 0 || value > 1) return KZG_GPU_ERR_ARG; ctx->opt_tail = (int)value; }
   else if (n == "team") { if (value < 0 || value > 1) return KZG_GPU_ERR_ARG; ctx->opt_team = (int)value; }
   else if (n == "affine_levels") { if (value < -1 || value > 4) return KZG_GPU_ERR_ARG; ctx->opt_affine_levels = (int)value; }
   else if (n == "setup_g2") ctx->opt_setup_g2 = value ? 1 : 0;

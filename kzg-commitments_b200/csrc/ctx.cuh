@@ -22,6 +22,7 @@
 #include "msm.cuh"
 #include "msm_affine.cuh"
 #include "msm_team.cuh"
+#include "msm_tail.cuh"
 #include "poly.cuh"
 #include "setup.cuh"
 
@@ -71,7 +72,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -96,6 +97,31 @@ struct kzg_gpu_ctx {
   virtual int selftest(int* failures) = 0;
   virtual int phase_times(float* ms, int n) = 0;
   virtual int msm_stats(uint64_t* out, int n) = 0;
+
+  // Cooperative launches (msm_tail.cuh): every CTA must be resident, so the grid is capped at what the occupancy
+  // calculator allows for that kernel on this device (cached per kernel).
+  std::map<const void*, int> coop_blocks;
+  int num_sms = 0;
+  int max_cooperative_blocks(const void* kernel, int threads) {
+    auto it = coop_blocks.find(kernel);
+    if (it != coop_blocks.end()) return it->second;
+    if (!num_sms && cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) num_sms = 0;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess) per_sm = 0;
+    const int v = per_sm * num_sms;
+    coop_blocks[kernel] = v;
+    return v;
+  }
+  int launch_cooperative(const void* kernel, uint64_t blocks_wanted, int threads, void* args_struct) {
+    const int cap = max_cooperative_blocks(kernel, threads);
+    if (cap <= 0) { last_error = "cooperative launch: kernel does not fit the device"; return KZG_GPU_ERR_CUDA; }
+    const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(blocks_wanted, (uint64_t)cap));
+    void* params[1] = {args_struct};
+    cudaError_t e = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3((unsigned)threads), params, 0, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchCooperativeKernel");
+    launches++;
+    return KZG_GPU_OK;
+  }
 
   int cuda_fail(cudaError_t e, const char* where) {
     char buf[256];
@@ -307,6 +333,12 @@ struct Ctx final : kzg_gpu_ctx {
     return KZG_GPU_OK;
   }
 
+  // 4-lane teams of one msm_tail<F> launch at full cooperative size
+  template <class F>
+  uint64_t tail_teams() {
+    return (uint64_t)max_cooperative_blocks((const void*)msm_tail<F>, TAIL_THREADS) * (TAIL_THREADS / 4);
+  }
+
   void phase_mark(int i) {
     if (opt_profile && phase_ev[0]) cudaEventRecord(phase_ev[i], stream);
   }
@@ -373,7 +405,26 @@ struct Ctx final : kzg_gpu_ctx {
     uint32_t* d_hist_cursor = d_hist_start + (MSM_MAX_CHUNK + 1);
 
     const int sms = 148;
+    // Small and medium MSMs (and the narrow end of every large one) run their many short steps inside two
+    // persistent cooperative kernels (msm_tail.cuh) instead of ~50 launches: "tail" option, on by default.
+    const bool use_tail = opt_tail && opt_team;
+    const bool fused_sort = use_tail && chunk_slices <= 1 && levels == 0 && records <= (1ull << 22) && nbuckets <= (1ull << 22);
     phase_mark(0);
+    int rc = KZG_GPU_OK;
+    const uint32_t* seg_off = starts.as<uint32_t>();
+    const uint32_t* seg_sorted = sorted.as<uint32_t>();
+    const Affine<F>* seg_pts = precomp ? table : bases;
+    if (fused_sort) {
+      chunk_slices = 0;
+      const uint64_t ntiles = (nbuckets + SCAN_TILE - 1) / SCAN_TILE;
+      CK(tile_sums.ensure((ntiles + 1) * 4));
+      SortArgs sa{sh, d_scalars, digits.as<int32_t>(), ranks.as<uint32_t>(), counts.as<uint32_t>(), starts.as<uint32_t>(),
+                  task_first.as<uint32_t>(), sorted.as<uint32_t>(), tile_sums.as<uint32_t>(), d_hist, d_hist_start,
+                  d_hist_cursor, tasks.as<MsmTask>(), slot_seg.as<MsmSlotSeg>(), nbuckets, sh.chunk};
+      const uint64_t want = (std::max<uint64_t>(records, nbuckets) + SCAN_THREADS - 1) / SCAN_THREADS;
+      rc = launch_cooperative((const void*)msm_sort_small<C>, want, SCAN_THREADS, &sa);
+      if (rc) return rc;
+    } else {
     CK(cudaMemsetAsync(counts.p, 0, (nbuckets + 1) * 4, stream));
     CK(cudaMemsetAsync(hist.p, 0, (MSM_MAX_CHUNK + 2) * 4, stream));
     {
@@ -389,7 +440,7 @@ struct Ctx final : kzg_gpu_ctx {
       }
       chunk_slices = 0;
     }
-    int rc = enqueue_scan(nbuckets, 0, counts.as<uint32_t>(), starts.as<uint32_t>(), nullptr);
+    rc = enqueue_scan(nbuckets, 0, counts.as<uint32_t>(), starts.as<uint32_t>(), nullptr);
     if (rc) return rc;
     {
       unsigned grid = (unsigned)std::min<uint64_t>((records + 255) / 256, (uint64_t)sms * 32);
@@ -398,9 +449,6 @@ struct Ctx final : kzg_gpu_ctx {
       LAUNCHED();
     }
     // batched-affine pre-reduction (G1 only): `levels` rounds of pairwise affine additions inside the buckets
-    const uint32_t* seg_off = starts.as<uint32_t>();
-    const uint32_t* seg_sorted = sorted.as<uint32_t>();
-    const Affine<F>* seg_pts = precomp ? table : bases;
     if constexpr (std::is_same<F, Fp>::value) {
       for (int l = 1; l <= levels; l++) {
         uint32_t* off_l = aff_off.as<uint32_t>() + (size_t)(l - 1) * (nbuckets + 1);
@@ -436,6 +484,7 @@ struct Ctx final : kzg_gpu_ctx {
                                                slot_seg.as<MsmSlotSeg>());
       LAUNCHED();
     }
+    }
     phase_mark(1);
     {
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)1 << 30);
@@ -444,11 +493,48 @@ struct Ctx final : kzg_gpu_ctx {
       LAUNCHED();
     }
     phase_mark(2);
-    {
-      // a bucket holds at most `count` records (count * W with the window table, where all windows share one
-      // bucket space), i.e. at most ceil(that / chunk) + 1 tasks; levels
-      // beyond the largest task count actually present (max_nt, on the device) return at once, so their grid is
-      // kept small: the pairs of a level are few and found by a grid-stride scan of slot_seg
+    XYZZ<F>*rin = red0.as<XYZZ<F>>(), *rout = red1.as<XYZZ<F>>(), *cin = red2.as<XYZZ<F>>(), *cout = red3.as<XYZZ<F>>();
+    const uint64_t Lr = Cn >= 2 ? Cn / 2 : 1, Lc = R >= 2 ? R / 2 : 1;
+    const uint64_t Pr = R >= WCHUNK ? R / WCHUNK : 1, Pc = Cn >= WCHUNK ? Cn / WCHUNK : 1;
+    // The reduction is a fixed sequence of steps whose item counts only shrink.  Steps wider than the tail
+    // kernel's team count are machine-filling launches of their own; from the first step that fits, everything
+    // that is left runs inside ONE cooperative kernel (msm_tail) with grid barriers between the steps.
+    const uint64_t tail_cap = use_tail ? 2 * tail_teams<F>() : 0;
+    const bool finish_in_tail = use_tail && batch <= 4096;  // one MSM per warp (see msm_tail)
+    TailArgs<F> ta{};
+    ta.ntasks_ptr = task_first.as<uint32_t>() + nbuckets;
+    ta.max_nt = d_hist + MSM_MAX_CHUNK + 1;
+    ta.slot_seg = slot_seg.as<MsmSlotSeg>();
+    ta.partial = partial.as<XYZZ<F>>();
+    ta.task_first = task_first.as<uint32_t>();
+    ta.nb = (uint64_t)sh.nb;
+    ta.groups = groups; ta.R = R; ta.Cn = Cn; ta.h = h;
+    ta.group_out = group_out.as<XYZZ<F>>();
+    ta.batch = batch; ta.groups_per_msm = sh.groups_per_msm; ta.c = sh.c; ta.modbytes = M; ta.want_affine = opt_finish_affine;
+    ta.out_bytes = out_bytes.as<uint8_t>(); ta.is_inf = out_inf.as<int>(); ta.out_xyzz = out_xyzz.as<XYZZ<F>>();
+    auto launch_tail = [&](int first, int last, uint64_t r_len, uint64_t c_len, uint64_t items) -> int {
+      ta.first_stage = first; ta.last_stage = last;
+      ta.rin = rin; ta.rout = rout; ta.cin = cin; ta.cout = cout;
+      ta.r_len = r_len; ta.c_len = c_len;
+      if (first <= TAIL_FOLD) items = std::max<uint64_t>(items, std::min<uint64_t>(max_tasks, tail_cap));
+      if (last >= TAIL_FINISH) items = std::max<uint64_t>(items, batch * 8);
+      return launch_cooperative((const void*)msm_tail<F>, (items * 4 + TAIL_THREADS - 1) / TAIL_THREADS, TAIL_THREADS, &ta);
+    };
+    const int tail_last = finish_in_tail ? TAIL_FINISH : TAIL_COMBINE;
+    bool in_tail = false;
+    // a bucket holds at most `count` records (count * W with the window table, where all windows share one
+    // bucket space), i.e. at most ceil(that / chunk) + 1 tasks; fold levels beyond the largest task count actually
+    // present (max_nt, on the device) are skipped
+    const uint64_t items_bp = groups * (R * Lr + Cn * Lc);
+    if (use_tail) {
+      if (items_bp <= tail_cap) {
+        rc = launch_tail(TAIL_FOLD, tail_last, 0, 0, items_bp);
+        in_tail = true;
+      } else {
+        rc = launch_tail(TAIL_FOLD, TAIL_FOLD, 0, 0, 0);  // all fold levels in one launch
+      }
+      if (rc) return rc;
+    } else {
       const uint64_t nt_bound = std::min<uint64_t>(max_tasks, count * (uint64_t)(precomp ? sh.W : 1) / (uint64_t)sh.chunk + 2);
       int fold_levels = 0;
       while ((1ull << fold_levels) < nt_bound && fold_levels < 31) fold_levels++;
@@ -464,9 +550,30 @@ struct Ctx final : kzg_gpu_ctx {
         LAUNCHED();
       }
     }
-    XYZZ<F>*rin = red0.as<XYZZ<F>>(), *rout = red1.as<XYZZ<F>>(), *cin = red2.as<XYZZ<F>>(), *cout = red3.as<XYZZ<F>>();
-    {
-      uint64_t Lr = Cn >= 2 ? Cn / 2 : 1, Lc = R >= 2 ? R / 2 : 1;
+    // one level of the two trees as its own launch; false once the level fits the tail kernel
+    auto wide_trees = [&](int stage, uint64_t sums0, uint64_t& len0, uint64_t sums1, uint64_t& len1) -> int {
+      while (len0 > 1 || len1 > 1) {
+        PairJob<F> j0{rin, rout, len0 > 1 ? sums0 * (len0 / 2) : 0};
+        PairJob<F> j1{cin, cout, len1 > 1 ? sums1 * (len1 / 2) : 0};
+        if (use_tail && j0.n_out + j1.n_out <= tail_cap) {
+          in_tail = true;
+          return launch_tail(stage, tail_last, len0, len1, j0.n_out + j1.n_out);
+        }
+        const uint64_t mx = std::max(j0.n_out, j1.n_out);
+        if (opt_team && j0.n_out + j1.n_out <= TEAM_MAX_ITEMS) {  // latency-bound level: 4 lanes per addition
+          dim3 grid((unsigned)((4 * mx + 127) / 128), 2);
+          msm_pair_sum_team<F><<<grid, 128, 0, stream>>>(j0, j1);
+        } else {
+          dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)148 * 64), 2);
+          msm_pair_sum<F><<<grid, 128, 0, stream>>>(j0, j1);
+        }
+        LAUNCHED();
+        if (len0 > 1) { std::swap(rin, rout); len0 /= 2; }
+        if (len1 > 1) { std::swap(cin, cout); len1 /= 2; }
+      }
+      return KZG_GPU_OK;
+    };
+    if (!in_tail) {
       BucketJob<F> jr{rin, R, Cn, Cn, 1, groups * R * Lr};
       BucketJob<F> jc{cin, Cn, R, 1, Cn, groups * Cn * Lc};
       const uint64_t mx = std::max(jr.total, jc.total);
@@ -478,34 +585,53 @@ struct Ctx final : kzg_gpu_ctx {
         msm_bucket_pairs<F><<<grid, 128, 0, stream>>>((uint64_t)sh.nb, task_first.as<uint32_t>(), partial.as<XYZZ<F>>(), jr, jc);
       }
       LAUNCHED();
-      rc = enqueue_pair_trees<F>(rin, rout, groups * R, Lr, cin, cout, groups * Cn, Lc);
-      if (rc) return rc;
-      // rin = row sums [groups * R], cin = column sums [groups * Cn]; weighted chunks, then trees again
-      const uint64_t Pr = R >= WCHUNK ? R / WCHUNK : 1, Pc = Cn >= WCHUNK ? Cn / WCHUNK : 1;
-      WeightedJob<F> wr{rin, rout, R, groups * Pr, 0u};
-      WeightedJob<F> wc{cin, cout, Cn, groups * Pc, 1u};
-      const uint64_t mw = std::max(wr.total, wc.total);
-      if (opt_team && wr.total + wc.total <= TEAM_MAX_ITEMS) {
-        dim3 gridw((unsigned)((4 * mw + 127) / 128), 2);
-        msm_weighted_chunks_team<F><<<gridw, 128, 0, stream>>>(wr, wc);
-      } else {
-        dim3 gridw((unsigned)std::min<uint64_t>((mw + 127) / 128, (uint64_t)sms * 64), 2);
-        msm_weighted_chunks<F><<<gridw, 128, 0, stream>>>(wr, wc);
-      }
-      LAUNCHED();
-      std::swap(rin, rout);
-      std::swap(cin, cout);
-      rc = enqueue_pair_trees<F>(rin, rout, groups, Pr, cin, cout, groups, Pc);
+      uint64_t r_len = Lr, c_len = Lc;
+      rc = wide_trees(TAIL_TREES1, groups * R, r_len, groups * Cn, c_len);
       if (rc) return rc;
     }
-    const XYZZ<F>*t1 = rin, *t2 = cin;
-    if (opt_team && groups <= TEAM_MAX_ITEMS)
-      msm_group_combine_team<F><<<(unsigned)((4 * groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
-    else
-      msm_group_combine<F><<<(unsigned)((groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
-    LAUNCHED();
+    if (!in_tail) {
+      // rin = row sums [groups * R], cin = column sums [groups * Cn]; weighted chunks, then trees again
+      WeightedJob<F> wr{rin, rout, R, groups * Pr, 0u};
+      WeightedJob<F> wc{cin, cout, Cn, groups * Pc, 1u};
+      if (use_tail && wr.total + wc.total <= tail_cap) {
+        in_tail = true;
+        rc = launch_tail(TAIL_WEIGHTED, tail_last, 0, 0, wr.total + wc.total);
+        if (rc) return rc;
+      } else {
+        const uint64_t mw = std::max(wr.total, wc.total);
+        if (opt_team && wr.total + wc.total <= TEAM_MAX_ITEMS) {
+          dim3 gridw((unsigned)((4 * mw + 127) / 128), 2);
+          msm_weighted_chunks_team<F><<<gridw, 128, 0, stream>>>(wr, wc);
+        } else {
+          dim3 gridw((unsigned)std::min<uint64_t>((mw + 127) / 128, (uint64_t)sms * 64), 2);
+          msm_weighted_chunks<F><<<gridw, 128, 0, stream>>>(wr, wc);
+        }
+        LAUNCHED();
+        std::swap(rin, rout);
+        std::swap(cin, cout);
+        uint64_t r_len = Pr, c_len = Pc;
+        rc = wide_trees(TAIL_TREES2, groups, r_len, groups, c_len);
+        if (rc) return rc;
+      }
+    }
+    if (!in_tail) {
+      const XYZZ<F>*t1 = rin, *t2 = cin;
+      if (use_tail && groups <= tail_cap && finish_in_tail) {
+        in_tail = true;
+        rc = launch_tail(TAIL_COMBINE, tail_last, 0, 0, groups);
+        if (rc) return rc;
+      } else {
+        if (opt_team && groups <= TEAM_MAX_ITEMS)
+          msm_group_combine_team<F><<<(unsigned)((4 * groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
+        else
+          msm_group_combine<F><<<(unsigned)((groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
+        LAUNCHED();
+      }
+    }
     phase_mark(3);
-    if (opt_team && sh.groups_per_msm > 1 && batch <= TEAM_MAX_ITEMS)  // Horner over the windows: a long dependent chain
+    if (in_tail && finish_in_tail) {
+      // Horner over the windows, affine normalisation and bytes ran at the end of the tail kernel
+    } else if (opt_team && sh.groups_per_msm > 1 && batch <= TEAM_MAX_ITEMS)  // Horner over the windows: a long dependent chain
       msm_finish_team<F><<<(unsigned)((4 * batch + 127) / 128), 128, 0, stream>>>(
           batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
           out_xyzz.as<XYZZ<F>>(), opt_finish_affine);
@@ -516,7 +642,7 @@ struct Ctx final : kzg_gpu_ctx {
           batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
           out_xyzz.as<XYZZ<F>>(), opt_finish_affine, lane_stride);
     }
-    LAUNCHED();
+    if (!(in_tail && finish_in_tail)) LAUNCHED();
     phase_mark(4);
     last_batch = batch;
     last_records = records; last_nbuckets = nbuckets; last_c = sh.c; last_chunk = sh.chunk;

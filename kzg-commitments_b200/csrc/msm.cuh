@@ -140,10 +140,12 @@ constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 KZG_HD uint32_t scan_value(uint32_t x, int chunk) { return chunk ? (x + (uint32_t)chunk - 1u) / (uint32_t)chunk : x; }
 #if defined(__CUDACC__)
-static __global__ void __launch_bounds__(SCAN_THREADS)
-scan_tile_sums(uint64_t n, int chunk, const uint32_t* __restrict__ in, uint32_t* __restrict__ tile_sums) {
+// The three phases as block-wide device bodies (tile = the block's tile index) so that the fused small-MSM sort
+// kernel (msm_tail.cuh) can run them between grid barriers; the __global__ wrappers are the large-MSM path.
+static __device__ __forceinline__ void scan_tile_sum_body(uint64_t n, int chunk, const uint32_t* __restrict__ in,
+                                                           uint32_t* __restrict__ tile_sums, uint64_t tile) {
   __shared__ uint32_t sm[SCAN_THREADS / 32];
-  const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
+  const uint64_t base = tile * SCAN_TILE;
   uint32_t a = 0;
 #pragma unroll
   for (int k = 0; k < SCAN_ITEMS; k++) {
@@ -156,11 +158,12 @@ scan_tile_sums(uint64_t n, int chunk, const uint32_t* __restrict__ in, uint32_t*
   if (threadIdx.x == 0) {
     uint32_t t = 0;
     for (int w = 0; w < SCAN_THREADS / 32; w++) t += sm[w];
-    tile_sums[blockIdx.x] = t;
+    tile_sums[tile] = t;
   }
+  __syncthreads();  // sm is reused by the caller's next tile
 }
-// one CTA: exclusive scan of tile_sums[0..ntiles) in place; total -> tile_sums[ntiles]
-static __global__ void __launch_bounds__(1024) scan_tiles(uint64_t ntiles, uint32_t* __restrict__ tile_sums) {
+// one CTA (any power-of-two blockDim <= 1024): exclusive scan of tile_sums[0..ntiles) in place; total -> tile_sums[ntiles]
+static __device__ __forceinline__ void scan_tiles_body(uint64_t ntiles, uint32_t* __restrict__ tile_sums) {
   __shared__ uint32_t s_part[1024];
   const int T = blockDim.x, tid = threadIdx.x;
   const uint64_t per = (ntiles + T - 1) / T;
@@ -183,12 +186,12 @@ static __global__ void __launch_bounds__(1024) scan_tiles(uint64_t ntiles, uint3
   }
   if (tid == T - 1) tile_sums[ntiles] = s_part[T - 1];
 }
-static __global__ void __launch_bounds__(SCAN_THREADS)
-scan_apply(uint64_t n, int chunk, const uint32_t* __restrict__ in, const uint32_t* __restrict__ tile_sums,
-           uint32_t* __restrict__ out, uint32_t* __restrict__ zero_me) {
+static __device__ __forceinline__ void scan_apply_body(uint64_t n, int chunk, const uint32_t* __restrict__ in,
+                                                        const uint32_t* __restrict__ tile_sums, uint32_t* __restrict__ out,
+                                                        uint32_t* __restrict__ zero_me, uint64_t tile, uint64_t ntiles) {
   __shared__ uint32_t sm[SCAN_THREADS];
   // thread t owns SCAN_ITEMS consecutive elements of the tile
-  const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
+  const uint64_t base = tile * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS], a = 0;
 #pragma unroll
   for (int k = 0; k < SCAN_ITEMS; k++) {
@@ -203,7 +206,7 @@ scan_apply(uint64_t n, int chunk, const uint32_t* __restrict__ in, const uint32_
     sm[threadIdx.x] += u;
     __syncthreads();
   }
-  uint32_t run = tile_sums[blockIdx.x] + sm[threadIdx.x] - a;
+  uint32_t run = tile_sums[tile] + sm[threadIdx.x] - a;
 #pragma unroll
   for (int k = 0; k < SCAN_ITEMS; k++) {
     if (base + k < n) {
@@ -212,7 +215,20 @@ scan_apply(uint64_t n, int chunk, const uint32_t* __restrict__ in, const uint32_
     }
     run += v[k];
   }
-  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) out[n] = tile_sums[gridDim.x];
+  if (tile == ntiles - 1 && threadIdx.x == 0) out[n] = tile_sums[ntiles];
+  __syncthreads();  // sm is reused by the caller's next tile
+}
+static __global__ void __launch_bounds__(SCAN_THREADS)
+scan_tile_sums(uint64_t n, int chunk, const uint32_t* __restrict__ in, uint32_t* __restrict__ tile_sums) {
+  scan_tile_sum_body(n, chunk, in, tile_sums, blockIdx.x);
+}
+static __global__ void __launch_bounds__(1024) scan_tiles(uint64_t ntiles, uint32_t* __restrict__ tile_sums) {
+  scan_tiles_body(ntiles, tile_sums);
+}
+static __global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply(uint64_t n, int chunk, const uint32_t* __restrict__ in, const uint32_t* __restrict__ tile_sums,
+           uint32_t* __restrict__ out, uint32_t* __restrict__ zero_me) {
+  scan_apply_body(n, chunk, in, tile_sums, out, zero_me, blockIdx.x, gridDim.x);
 }
 #endif
 
@@ -320,10 +336,9 @@ KZG_HD XYZZ<F> bucket_value(const uint32_t* task_first, const XYZZ<F>* partial, 
   return partial[t0];
 }
 #if defined(__CUDACC__)
-// task-length histogram, privatised in shared memory
-static __global__ void __launch_bounds__(256)
-msm_task_hist(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts, const uint32_t* __restrict__ task_first,
-              uint32_t* __restrict__ hist) {
+// task-length histogram, privatised in shared memory (block-wide body; grid-stride over the buckets)
+static __device__ __forceinline__ void msm_task_hist_body(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts,
+                                                           const uint32_t* __restrict__ task_first, uint32_t* __restrict__ hist) {
   __shared__ uint32_t sh[MSM_MAX_CHUNK + 2];
   for (int i = threadIdx.x; i <= MSM_MAX_CHUNK + 1; i += blockDim.x) sh[i] = 0;
   __syncthreads();
@@ -334,9 +349,14 @@ msm_task_hist(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts,
     if (sh[i]) atomicAdd(&hist[i], sh[i]);
   if (threadIdx.x == 0 && sh[MSM_MAX_CHUNK + 1]) atomicMax(&hist[MSM_MAX_CHUNK + 1], sh[MSM_MAX_CHUNK + 1]);
 }
-// hist (MSM_MAX_CHUNK+1 bins) -> exclusive starts; cursors cleared.  One warp is plenty.
-static __global__ void msm_task_hist_scan(const uint32_t* __restrict__ hist, uint32_t* __restrict__ hist_start,
-                                          uint32_t* __restrict__ cursor) {
+static __global__ void __launch_bounds__(256)
+msm_task_hist(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts, const uint32_t* __restrict__ task_first,
+              uint32_t* __restrict__ hist) {
+  msm_task_hist_body(nbuckets, chunk, starts, task_first, hist);
+}
+// hist (MSM_MAX_CHUNK+1 bins) -> exclusive starts; cursors cleared.  One thread is plenty.
+static __device__ __forceinline__ void msm_task_hist_scan_body(const uint32_t* __restrict__ hist, uint32_t* __restrict__ hist_start,
+                                                                uint32_t* __restrict__ cursor) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   uint32_t run = 0;
   for (int i = 0; i <= MSM_MAX_CHUNK; i++) {
@@ -345,12 +365,16 @@ static __global__ void msm_task_hist_scan(const uint32_t* __restrict__ hist, uin
     cursor[i] = 0;
   }
 }
+static __global__ void msm_task_hist_scan(const uint32_t* __restrict__ hist, uint32_t* __restrict__ hist_start,
+                                          uint32_t* __restrict__ cursor) {
+  msm_task_hist_scan_body(hist, hist_start, cursor);
+}
 // placement: a CTA first counts its tasks per bin in shared memory, reserves one range per bin with a
 // single global atomic, then its threads take slots inside the reserved ranges.
-static __global__ void __launch_bounds__(256)
-msm_task_place(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts, const uint32_t* __restrict__ task_first,
-               const uint32_t* __restrict__ hist_start, uint32_t* __restrict__ cursor, MsmTask* __restrict__ tasks,
-               MsmSlotSeg* __restrict__ slot_seg) {
+static __device__ __forceinline__ void msm_task_place_body(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts,
+                                                            const uint32_t* __restrict__ task_first,
+                                                            const uint32_t* __restrict__ hist_start, uint32_t* __restrict__ cursor,
+                                                            MsmTask* __restrict__ tasks, MsmSlotSeg* __restrict__ slot_seg) {
   __shared__ uint32_t cnt[MSM_MAX_CHUNK + 2], base[MSM_MAX_CHUNK + 1];
   for (uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x; b0 < nbuckets; b0 += (uint64_t)gridDim.x * blockDim.x) {
     for (int i = threadIdx.x; i <= MSM_MAX_CHUNK + 1; i += blockDim.x) cnt[i] = 0;
@@ -366,6 +390,12 @@ msm_task_place(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts
     if (b < nbuckets) msm_task_place_thread(chunk, starts, task_first, base, cnt, tasks, slot_seg, b);
     __syncthreads();
   }
+}
+static __global__ void __launch_bounds__(256)
+msm_task_place(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts, const uint32_t* __restrict__ task_first,
+               const uint32_t* __restrict__ hist_start, uint32_t* __restrict__ cursor, MsmTask* __restrict__ tasks,
+               MsmSlotSeg* __restrict__ slot_seg) {
+  msm_task_place_body(nbuckets, chunk, starts, task_first, hist_start, cursor, tasks, slot_seg);
 }
 template <class F>
 __global__ void __launch_bounds__(128, sizeof(F) <= 48 ? 4 : 1)
