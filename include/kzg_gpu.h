@@ -81,6 +81,13 @@ int kzg_gpu_srs_load(kzg_gpu_ctx* ctx, uint64_t n, const uint8_t* g1, const uint
 /* [s^i]G1 (n * 2M bytes) and [s^i]G2 (n * 4M bytes) for i < n from the secret s (SB little-endian
  * bytes); either output may be NULL.  The generated SRS is left resident (as after srs_load). */
 int kzg_gpu_setup_powers(kzg_gpu_ctx* ctx, const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out);
+/* The slice [first_index, first_index + n) of the same SRS: [s^(first_index + i)]G1 / G2, i < n, left resident as
+ * points 0..n-1 of this context.  This is generate_elements_range(start, end, ..) of the reference
+ * (src/trusted_setup.cpp:123-135: its std::thread fan-out over index ranges) with the device in place of a thread,
+ * and what the point-range split of one large MSM across GPUs loads on device g.
+ * The secret and its powers are zeroed in device memory before either call returns. */
+int kzg_gpu_setup_powers_range(kzg_gpu_ctx* ctx, const uint8_t* s_le, uint64_t first_index, uint64_t n, uint8_t* g1_out,
+                               uint8_t* g2_out);
 
 /* out = sum_{i<count} scalars[i] * G1[base_offset + i]   (host buffers) */
 int kzg_gpu_msm_g1(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t base_offset,
@@ -167,6 +174,45 @@ int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops_per_second);
  * independent formulations (e.g. (a+b)^2 = a^2+2ab+b^2, P+Q-Q = P, [r]G = inf).  Returns the number of
  * failed checks in *failures. */
 int kzg_gpu_selftest(kzg_gpu_ctx* ctx, int* failures);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Multi-GPU: a GROUP of devices of one box behind the same C ABI (SURVEY.md 8(b) "devices, n_devices" and 8(e)).
+ *
+ * Replaces the reference's only parallel construct on this path, the std::thread fan-out over index ranges
+ * (src/trusted_setup.cpp:39-73), with one device context + one host worker thread per GPU:
+ *   - independent units, no collective: the blobs of kzg_gpu_group_msm_g1_batch / _prove_batch are cut into
+ *     contiguous ranges, one per device, each against that device's replica of the SRS; every device reads its
+ *     slice straight from the caller's buffer and writes its results straight into the caller's arrays.
+ *   - one exchange step: kzg_gpu_group_msm_g1 over at least `split_min` points is split by contiguous POINT
+ *     RANGE; device g holds only its slice [g*n/G, (g+1)*n/G) of the SRS (with a window table sized for the slice),
+ *     leaves one projective partial sum, and the <= 8 partials (4*L words each) are folded and normalised on device 0
+ *     (kzg_gpu_g1_sum_partials).  One process drives all devices, so the exchange is G small D2H copies, not NCCL;
+ *     the one-process-per-GPU form of the same split (NCCL all-gather of the partials) is in bench.py / sharding.py.
+ * Calls on one group are serialised; different groups are independent.  No CPU fallback. */
+typedef struct kzg_gpu_group kzg_gpu_group;
+
+/* number of visible CUDA devices (0 when there is no driver or no device) */
+int kzg_gpu_device_count(void);
+/* devices == NULL: ordinals 0 .. n_devices-1 (n_devices <= 0: every visible device). */
+int kzg_gpu_group_create(kzg_gpu_group** out, int curve, const int* devices, int n_devices);
+void kzg_gpu_group_destroy(kzg_gpu_group* group);
+int kzg_gpu_group_size(const kzg_gpu_group* group);
+/* the context of member i holding the full (replicated) SRS: for the single-device entry points above */
+kzg_gpu_ctx* kzg_gpu_group_ctx(kzg_gpu_group* group, int i);
+const char* kzg_gpu_group_last_error(const kzg_gpu_group* group);
+/* kzg_gpu_set_option on every member context; additionally "split_min" (points from which a single MSM is split
+ * by point range, default 65536; must be set before the SRS is made resident). */
+int kzg_gpu_group_set_option(kzg_gpu_group* group, const char* name, long long value);
+/* as kzg_gpu_srs_load / kzg_gpu_setup_powers: the SRS becomes resident on every member (replica + range slice) */
+int kzg_gpu_group_srs_load(kzg_gpu_group* group, uint64_t n, const uint8_t* g1, const uint8_t* g2);
+int kzg_gpu_group_setup_powers(kzg_gpu_group* group, const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out);
+/* as kzg_gpu_msm_g1 / _batch / kzg_gpu_prove_batch, sharded over the members as described above */
+int kzg_gpu_group_msm_g1(kzg_gpu_group* group, const uint8_t* scalars, uint64_t count, uint64_t base_offset,
+                         uint8_t* out_xy /* 2M */, int* is_inf);
+int kzg_gpu_group_msm_g1_batch(kzg_gpu_group* group, const uint8_t* scalars, uint64_t count, uint64_t batch,
+                               uint8_t* out_xy, int* is_inf);
+int kzg_gpu_group_prove_batch(kzg_gpu_group* group, const uint8_t* coeffs, uint64_t n, const int64_t* first_roots,
+                              uint64_t k, uint64_t batch, uint8_t* out_xy, int* is_inf);
 
 #ifdef __cplusplus
 }

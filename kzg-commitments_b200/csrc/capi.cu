@@ -36,6 +36,12 @@ int kzg_gpu_scalar_bytes(int curve) {
   }
 }
 
+int kzg_gpu_device_count(void) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return ndev;
+}
+
 int kzg_gpu_ctx_create(kzg_gpu_ctx** out, int curve, int device) {
   if (!out) return KZG_GPU_ERR_ARG;
   *out = nullptr;
@@ -82,7 +88,11 @@ int kzg_gpu_srs_load(kzg_gpu_ctx* ctx, uint64_t n, const uint8_t* g1, const uint
   return ctx->srs_load(n, g1, g2);
 }
 int kzg_gpu_setup_powers(kzg_gpu_ctx* ctx, const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) {
-  return ctx ? ctx->setup_powers(s_le, n, g1_out, g2_out) : KZG_GPU_ERR_ARG;
+  return ctx ? ctx->setup_powers(s_le, 0, n, g1_out, g2_out) : KZG_GPU_ERR_ARG;
+}
+int kzg_gpu_setup_powers_range(kzg_gpu_ctx* ctx, const uint8_t* s_le, uint64_t first_index, uint64_t n, uint8_t* g1_out,
+                               uint8_t* g2_out) {
+  return ctx ? ctx->setup_powers(s_le, first_index, n, g1_out, g2_out) : KZG_GPU_ERR_ARG;
 }
 int kzg_gpu_msm_g1(kzg_gpu_ctx* ctx, const uint8_t* scalars, uint64_t count, uint64_t base_offset, uint8_t* out_xy, int* is_inf) {
   return ctx ? ctx->msm(1, scalars, false, count, 1, base_offset, out_xy, is_inf, true) : KZG_GPU_ERR_ARG;

@@ -77,7 +77,7 @@ struct kzg_gpu_ctx {
 
   virtual ~kzg_gpu_ctx() {}
   virtual int srs_load(uint64_t n, const uint8_t* g1, const uint8_t* g2) = 0;
-  virtual int setup_powers(const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) = 0;
+  virtual int setup_powers(const uint8_t* s_le, uint64_t first_index, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) = 0;
   virtual int msm(int group, const uint8_t* scalars, bool scalars_on_device, uint64_t count, uint64_t batch,
                   uint64_t base_offset, uint8_t* out, int* is_inf, bool fetch) = 0;
   virtual int fetch(uint8_t* out, int* is_inf) = 0;
@@ -1137,10 +1137,29 @@ struct Ctx final : kzg_gpu_ctx {
     return KZG_GPU_OK;
   }
 
-  int setup_powers(const uint8_t* s_le, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) override {
+  // Zero the buffers that held the secret and its powers (the reference frees s_powers when its constructor returns,
+  // src/trusted_setup.cpp:21-74; here they would otherwise stay in HBM for the lifetime of the context).
+  int scrub_secret(uint64_t n) {
+    if (scal.p) cudaMemsetAsync(scal.p, 0, std::min<size_t>(scal.cap, 64), stream);
+    if (powers.p) cudaMemsetAsync(powers.p, 0, std::min<size_t>(powers.cap, n * sizeof(Fr)), stream);
+    if (fb_sums.p) cudaMemsetAsync(fb_sums.p, 0, fb_sums.cap, stream);
+    cudaError_t e = cudaStreamSynchronize(stream);
+    powers.release();
+    if (fb_sums.cap > ((size_t)64 << 20)) fb_sums.release();  // 192 / 384 B per index: not kept next to a large SRS
+    return e == cudaSuccess ? KZG_GPU_OK : cuda_fail(e, "scrub_secret");
+  }
+  int setup_powers(const uint8_t* s_le, uint64_t first_index, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) override {
     std::lock_guard<std::recursive_mutex> lock(mu);
     CK(cudaSetDevice(device));
-    if (!s_le || n == 0) return KZG_GPU_ERR_ARG;
+    if (!s_le || n == 0 || first_index + n < n) return KZG_GPU_ERR_ARG;
+    const int rc_run = setup_powers_locked(s_le, first_index, n, g1_out, g2_out);
+    const int rc_scrub = scrub_secret(n);  // on every exit
+    if (rc_run) return rc_run;
+    if (rc_scrub) return rc_scrub;
+    srs_n = n;
+    return build_table();
+  }
+  int setup_powers_locked(const uint8_t* s_le, uint64_t first_index, uint64_t n, uint8_t* g1_out, uint8_t* g2_out) {
     int rc = ensure_fixed_base_tables();
     if (rc) return rc;
     CK(stage.ensure(std::max<size_t>(n * (size_t)(4 * M), 64)));
@@ -1150,7 +1169,7 @@ struct Ctx final : kzg_gpu_ctx {
     CK(cudaMemcpyAsync(scal.p, s_le, SB, cudaMemcpyHostToDevice, stream));
     const int per_thread = 32;
     const uint64_t nthreads = (n + per_thread - 1) / per_thread;
-    setup_powers_kernel<C><<<(unsigned)((nthreads + 63) / 64), 64, 0, stream>>>(n, scal.as<uint8_t>(), per_thread, powers.as<uint32_t>());
+    setup_powers_kernel<C><<<(unsigned)((nthreads + 63) / 64), 64, 0, stream>>>(n, first_index, scal.as<uint8_t>(), per_thread, powers.as<uint32_t>());
     LAUNCHED();
     const unsigned grid = (unsigned)((n + 127) / 128);
     const unsigned grid_aff = (unsigned)(((n + FB_BATCH - 1) / FB_BATCH + 127) / 128);
@@ -1173,10 +1192,8 @@ struct Ctx final : kzg_gpu_ctx {
       if (g2_out) CK(cudaMemcpyAsync(g2_out, stage.p, n * (size_t)(4 * M), cudaMemcpyDeviceToHost, stream));
       CK(cudaStreamSynchronize(stream));
     }
-    if (fb_sums.cap > ((size_t)64 << 20)) fb_sums.release();  // 192 / 384 B per index: not kept next to a large SRS
-    srs_n = n;
     have_g2 = want_g2;
-    return build_table();
+    return KZG_GPU_OK;
   }
 
   // ------------------------------------------------------------------ diagnostics

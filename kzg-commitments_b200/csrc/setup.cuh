@@ -18,10 +18,10 @@ constexpr int FB_HALF = 1 << (FB_C - 1);      // 128 table entries per window
 template <class C>
 KZG_HD constexpr int fb_windows() { return (C::SCALAR_BITS + 1 + FB_C - 1) / FB_C; }
 
-// powers[i] = s^i (canonical little-endian words, NOT Montgomery), i < n.
-// Thread t produces indices [t*S, (t+1)*S): s^(t*S) by square-and-multiply, then S-1 products.
+// powers[i] = s^(first_index + i) (canonical little-endian words, NOT Montgomery), i < n.
+// Thread t produces indices [t*S, (t+1)*S): s^(first_index + t*S) by square-and-multiply, then S-1 products.
 template <class C>
-__global__ void setup_powers_kernel(uint64_t n, const uint8_t* __restrict__ s_bytes, int per_thread,
+__global__ void setup_powers_kernel(uint64_t n, uint64_t first_index, const uint8_t* __restrict__ s_bytes, int per_thread,
                              uint32_t* __restrict__ powers /* n * FrP::L words */) {
   using Fr = Field<typename C::FrP>;
   const uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
@@ -34,9 +34,9 @@ __global__ void setup_powers_kernel(uint64_t n, const uint8_t* __restrict__ s_by
 #pragma unroll
   for (int i = 0; i < Fr::L; i++) s.v[i] = k[i];
   s = Fr::to_mont(s);
-  // s^lo, lo < 2^64
+  // s^(first_index + lo), exponent < 2^64
   Fr cur = Fr::one(), base = s;
-  for (uint64_t e = lo; e; e >>= 1) {
+  for (uint64_t e = first_index + lo; e; e >>= 1) {
     if (e & 1) cur = Fr::mul(cur, base);
     base = Fr::sqr(base);
   }

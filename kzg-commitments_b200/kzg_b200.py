@@ -56,6 +56,7 @@ def load_library():
         "kzg_gpu_set_option": (ctypes.c_int, [vp, ctypes.c_char_p, ctypes.c_longlong]),
         "kzg_gpu_srs_load": (ctypes.c_int, [vp, u64, u8p, u8p]),
         "kzg_gpu_setup_powers": (ctypes.c_int, [vp, u8p, u64, u8p, u8p]),
+        "kzg_gpu_setup_powers_range": (ctypes.c_int, [vp, u8p, u64, u64, u8p, u8p]),
         "kzg_gpu_msm_g1": (ctypes.c_int, [vp, vp, u64, u64, u8p, ip]),
         "kzg_gpu_msm_g2": (ctypes.c_int, [vp, vp, u64, u64, u8p, ip]),
         "kzg_gpu_msm_g1_batch": (ctypes.c_int, [vp, vp, u64, u64, u8p, ip]),
@@ -71,6 +72,18 @@ def load_library():
         "kzg_gpu_interpolate_range": (ctypes.c_int, [vp, u8p, i64, u64, u8p, u8p]),
         "kzg_gpu_commit_bytes": (ctypes.c_int, [vp, vp, u64, ctypes.c_int, i64, u8p, u8p, ctypes.POINTER(ctypes.c_int)]),
         "kzg_gpu_prove_batch": (ctypes.c_int, [vp, vp, u64, ctypes.POINTER(ctypes.c_int64), u64, u64, u8p, ip]),
+        "kzg_gpu_device_count": (ctypes.c_int, []),
+        "kzg_gpu_group_create": (ctypes.c_int, [ctypes.POINTER(vp), ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int]),
+        "kzg_gpu_group_destroy": (None, [vp]),
+        "kzg_gpu_group_size": (ctypes.c_int, [vp]),
+        "kzg_gpu_group_ctx": (vp, [vp, ctypes.c_int]),
+        "kzg_gpu_group_last_error": (ctypes.c_char_p, [vp]),
+        "kzg_gpu_group_set_option": (ctypes.c_int, [vp, ctypes.c_char_p, ctypes.c_longlong]),
+        "kzg_gpu_group_srs_load": (ctypes.c_int, [vp, u64, u8p, u8p]),
+        "kzg_gpu_group_setup_powers": (ctypes.c_int, [vp, u8p, u64, u8p, u8p]),
+        "kzg_gpu_group_msm_g1": (ctypes.c_int, [vp, vp, u64, u64, u8p, ip]),
+        "kzg_gpu_group_msm_g1_batch": (ctypes.c_int, [vp, vp, u64, u64, u8p, ip]),
+        "kzg_gpu_group_prove_batch": (ctypes.c_int, [vp, vp, u64, ctypes.POINTER(ctypes.c_int64), u64, u64, u8p, ip]),
         "kzg_gpu_ctx_stream": (vp, [vp]),
         "kzg_gpu_launch_count": (u64, [vp]),
         "kzg_gpu_microbench": (ctypes.c_int, [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
@@ -93,7 +106,10 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_msm_fetch_partial", "kzg_gpu_g1_sum_partials", "kzg_gpu_poly_quotient", "kzg_gpu_poly_eval_range",
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
     "kzg_gpu_phase_times", "kzg_gpu_msm_stats", "kzg_gpu_msm_partial_device", "kzg_gpu_g1_sum_partials_device",
-    "kzg_gpu_interpolate_range", "kzg_gpu_prove_batch", "kzg_gpu_commit_bytes",
+    "kzg_gpu_interpolate_range", "kzg_gpu_prove_batch", "kzg_gpu_commit_bytes", "kzg_gpu_setup_powers_range",
+    "kzg_gpu_device_count", "kzg_gpu_group_create", "kzg_gpu_group_destroy", "kzg_gpu_group_size", "kzg_gpu_group_ctx",
+    "kzg_gpu_group_last_error", "kzg_gpu_group_set_option", "kzg_gpu_group_srs_load", "kzg_gpu_group_setup_powers",
+    "kzg_gpu_group_msm_g1", "kzg_gpu_group_msm_g1_batch", "kzg_gpu_group_prove_batch",
 ]
 
 
@@ -157,11 +173,12 @@ class Context:
         self._check(self.lib.kzg_gpu_srs_load(self.h, n, g1, g2), "srs_load")
         self.srs_n = n
 
-    def setup_powers(self, s, n, want_bytes=True):
+    def setup_powers(self, s, n, want_bytes=True, first_index=0):
+        """[s^(first_index + i)]G1 / G2, i < n, left resident (first_index > 0: one device's slice of a shared SRS)."""
         s_le = (int(s) % self.r).to_bytes(self.SB, "little")
         g1 = ctypes.create_string_buffer(n * 2 * self.M) if want_bytes else None
         g2 = ctypes.create_string_buffer(n * 4 * self.M) if want_bytes else None
-        self._check(self.lib.kzg_gpu_setup_powers(self.h, s_le, n, g1, g2), "setup_powers")
+        self._check(self.lib.kzg_gpu_setup_powers_range(self.h, s_le, first_index, n, g1, g2), "setup_powers")
         self.srs_n = n
         return (g1.raw, g2.raw) if want_bytes else (None, None)
 
@@ -298,6 +315,80 @@ class Context:
         f = ctypes.c_int(-1)
         self._check(self.lib.kzg_gpu_selftest(self.h, ctypes.byref(f)), "selftest")
         return f.value
+
+
+class Group:
+    """kzg_gpu_group: several devices of one box behind the C ABI (one process).  Blob batches are sharded by blob,
+    a single large MSM by point range (include/kzg_gpu.h "Multi-GPU")."""
+
+    def __init__(self, curve, devices=None):
+        self.lib = load_library()
+        self.curve = CURVE_IDS[curve.lower()] if isinstance(curve, str) else int(curve)
+        self.M = self.lib.kzg_gpu_modbytes(self.curve)
+        self.SB = self.lib.kzg_gpu_scalar_bytes(self.curve)
+        self.r = CURVE_ORDER[self.curve]
+        h = ctypes.c_void_p()
+        if devices is None or isinstance(devices, int):
+            rc = self.lib.kzg_gpu_group_create(ctypes.byref(h), self.curve, None, int(devices or 0))
+        else:
+            arr = (ctypes.c_int * len(devices))(*devices)
+            rc = self.lib.kzg_gpu_group_create(ctypes.byref(h), self.curve, arr, len(devices))
+        if rc != 0:
+            raise RuntimeError("kzg_gpu_group_create failed: %s (CUDA devices are required; no CPU fallback)"
+                               % self.lib.kzg_gpu_strerror(rc).decode())
+        self.h = h
+        self.size = self.lib.kzg_gpu_group_size(h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.kzg_gpu_group_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError("%s failed: %s [%s]" % (what, self.lib.kzg_gpu_strerror(rc).decode(),
+                                                       self.lib.kzg_gpu_group_last_error(self.h).decode()))
+
+    def set_option(self, name, value):
+        self._check(self.lib.kzg_gpu_group_set_option(self.h, name.encode(), int(value)), "group set_option " + name)
+
+    def srs_load(self, g1, g2=None):
+        n = len(g1) // (2 * self.M)
+        self._check(self.lib.kzg_gpu_group_srs_load(self.h, n, g1, g2), "group srs_load")
+
+    def setup_powers(self, s, n, want_bytes=True):
+        s_le = (int(s) % self.r).to_bytes(self.SB, "little")
+        g1 = ctypes.create_string_buffer(n * 2 * self.M) if want_bytes else None
+        g2 = ctypes.create_string_buffer(n * 4 * self.M) if want_bytes else None
+        self._check(self.lib.kzg_gpu_group_setup_powers(self.h, s_le, n, g1, g2), "group setup_powers")
+        return (g1.raw, g2.raw) if want_bytes else (None, None)
+
+    def msm_g1(self, scalars, count=None, base_offset=0):
+        count = len(scalars) // self.SB if count is None else count
+        out = ctypes.create_string_buffer(2 * self.M)
+        inf = ctypes.c_int(0)
+        self._check(self.lib.kzg_gpu_group_msm_g1(self.h, _ptr(scalars), count, base_offset, out, ctypes.byref(inf)), "group msm_g1")
+        return out.raw, bool(inf.value)
+
+    def msm_g1_batch(self, scalars, count, batch):
+        out = ctypes.create_string_buffer(batch * 2 * self.M)
+        inf = (ctypes.c_int * batch)()
+        self._check(self.lib.kzg_gpu_group_msm_g1_batch(self.h, _ptr(scalars), count, batch, out, inf), "group msm_g1_batch")
+        return out.raw, [bool(v) for v in inf]
+
+    def prove_batch(self, coeffs, n, first_roots, k):
+        batch = len(first_roots)
+        out = ctypes.create_string_buffer(batch * 2 * self.M)
+        inf = (ctypes.c_int * batch)()
+        roots = (ctypes.c_int64 * batch)(*first_roots)
+        self._check(self.lib.kzg_gpu_group_prove_batch(self.h, _ptr(coeffs), n, roots, k, batch, out, inf), "group prove_batch")
+        return out.raw, [bool(v) for v in inf]
 
 
 # ------------------------------------------------------------------------------------------------

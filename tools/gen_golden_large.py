@@ -20,7 +20,6 @@ Writes tests/golden/<curve>/kat_large.json.
 import hashlib
 import json
 import os
-import re
 import subprocess
 import sys
 import tempfile
@@ -29,15 +28,11 @@ from multiprocessing import Pool
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from oracle.kzg_oracle import get_curve  # noqa: E402
+from tests.golden_util import chunk_values, ref_from_hex, stream_scalars  # noqa: E402
 
 REF_TESTING = "/root/reference/testing"
 STR_149 = ("wrgJKdE3t5bECALy3eKIwYxEF3V7Z8KTx0nFe1IX5tjH22F5gXOa5LnIMIQuOiNJj8YL8rqDiZSkZfoEDAmGTXXqqvkCd5WKE2fMtVXa2zKae6opGY4i6bY"
            "uUG67LaSXd5tUbO4bNPB0TxnkWrSaQ")  # testing/testing.cpp:233 (150 characters -> degree 149)
-
-
-def stream_scalars(r, seed, n):
-    """c_i = sha256(seed | i) mod r — a recipe any test can replay without storing 4097 x 32 bytes."""
-    return [int.from_bytes(hashlib.sha256(b"%s|%d" % (seed.encode(), i)).digest() * 2, "big") % r for i in range(n)]
 
 
 def _setup_chunk(args):
@@ -65,24 +60,8 @@ def make_srs(cname, s, n, path):
     return hashlib.sha256(raw).hexdigest()
 
 
-def ref_from_hex(text):
-    """testing/testing.cpp:406-413 from_hex, faithfully: two characters at a time through strtol(.., 16), so a
-    trailing newline contributes a zero byte (blob1.txt) and a dangling single digit is a byte of its own (blob2.txt)."""
-    out = bytearray()
-    for i in range(0, len(text), 2):
-        m = re.match(r"\s*([0-9a-fA-F]*)", text[i:i + 2])
-        out.append(int(m.group(1), 16) & 0xFF if m.group(1) else 0)
-    return bytes(out)
-
-
 def run(binary, *args):
     return subprocess.run([binary, *map(str, args)], check=True, capture_output=True, text=True).stdout
-
-
-def chunk_bytes(C, data, chunk):
-    pad = chunk - (len(data) % chunk)  # eth_blob_test pads a FULL chunk when already aligned (testing.cpp:63-65)
-    data = data + bytes(pad)
-    return [int.from_bytes(data[i:i + chunk], "little") for i in range(0, len(data), chunk)]
 
 
 def main():
@@ -113,7 +92,7 @@ def main():
                       ("coeffs", stream_scalars(C.r, "deg4096-" + cname, 4097))))
         for bname in ("blob1", "blob2"):
             data = ref_from_hex(open(os.path.join(REF_TESTING, bname + ".txt")).read())
-            ys = chunk_bytes(C, data, chunk)
+            ys = chunk_values(data, chunk)
             if len(ys) + 1 < cfg["n"]:
                 polys.append((bname, {"kind": "blob_file", "file": bname + ".txt", "chunk": chunk, "sha256_bytes":
                                       hashlib.sha256(data).hexdigest(), "chunks": len(ys)}, ("ys", ys)))
