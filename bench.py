@@ -368,7 +368,7 @@ def run_b200(args):
     # ---------------- strong scaling: ONE MSM split N ways, 4096 blobs IN TOTAL
     strong = {}
     if not args.no_strong:
-        for lg in (20, 22):
+        for lg in [int(x) for x in args.strong_log2n.split(",") if x]:
             if lg == args.log2n and world == 1:
                 strong["msm_2p%d" % lg] = {"points": n, "ms": ms_per_step, "points_per_s": n / (ms_per_step * 1e-3),
                                            "e2e_ms": e2e_ms_per_step, "e2e_points_per_s": n / (e2e_ms_per_step * 1e-3),
@@ -637,6 +637,7 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=16384, help="terms per reference process per step")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-strong", action="store_true")
+    ap.add_argument("--strong-log2n", default="20,22", help="sizes of the single MSMs split N ways (strong scaling)")
     ap.add_argument("--no-secondary", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

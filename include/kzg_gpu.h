@@ -193,7 +193,8 @@ typedef struct kzg_gpu_group kzg_gpu_group;
 
 /* number of visible CUDA devices (0 when there is no driver or no device) */
 int kzg_gpu_device_count(void);
-/* devices == NULL: ordinals 0 .. n_devices-1 (n_devices <= 0: every visible device). */
+/* devices == NULL: ordinals 0 .. n_devices-1 (n_devices <= 0: every visible device).  An ordinal may be listed more
+ * than once (members sharing a device). */
 int kzg_gpu_group_create(kzg_gpu_group** out, int curve, const int* devices, int n_devices);
 void kzg_gpu_group_destroy(kzg_gpu_group* group);
 int kzg_gpu_group_size(const kzg_gpu_group* group);
