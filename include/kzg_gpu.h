@@ -53,7 +53,8 @@ enum kzg_gpu_status {
 };
 
 const char* kzg_gpu_strerror(int status);
-/* last CUDA error text recorded on this context (empty string if none) */
+/* error text of the most recent call on this context (empty string after a successful call); the pointer stays valid
+ * until the next call on the same context */
 const char* kzg_gpu_last_error(const kzg_gpu_ctx* ctx);
 
 /* sizes for a curve: M (MODBYTES_CURVE) and SB (CURVE_ORDER_BYTES); < 0 for an unknown curve */
@@ -145,7 +146,8 @@ int kzg_gpu_interpolate_range(kzg_gpu_ctx* ctx, const uint8_t* ys, int64_t first
 /* Document bytes to commitment without leaving the device: blob::from_bytes (src/blob.cpp:19-48: chunk i of chunk_size
  * bytes, zero-padded, little-endian, at node chunk_offset + i) -> poly::from_blob (src/poly.cpp:4-6) -> create_commit
  * (src/trusted_setup.cpp:137-147).  chunk_size in 1..SB-1 (MAX_CHUNK_BYTES, src/kzg.h:31) and byte_length a multiple of
- * it, else KZG_GPU_ERR_ARG (the reference throws invalid_argument); byte_length / chunk_size <= SRS size.
+ * it, else KZG_GPU_ERR_ARG (the reference throws invalid_argument); byte_length / chunk_size < SRS size (the bound of
+ * create_commit, src/trusted_setup.cpp:138).
  * coeffs_out: NULL or byte_length/chunk_size * SB bytes receiving the polynomial (for later create_proof calls). */
 int kzg_gpu_commit_bytes(kzg_gpu_ctx* ctx, const uint8_t* bytes, uint64_t byte_length, int chunk_size, int64_t chunk_offset,
                          uint8_t* coeffs_out, uint8_t* out_xy /* 2M */, int* is_inf);

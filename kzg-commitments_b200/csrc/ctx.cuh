@@ -243,7 +243,10 @@ struct Ctx final : kzg_gpu_ctx {
     if (!opt_precompute) return reserve_scratch();
     const int c = pick_table_c(srs_n);
     const int W = (C::SCALAR_BITS + 1 + c - 1) / c;
-    if (W > MAXW) return KZG_GPU_ERR_ARG;
+    if (W > MAXW) {
+      last_error = "window_bits is too small for the per-SRS window table (more than 40 windows); use precompute = 0 with it";
+      return KZG_GPU_ERR_ARG;
+    }
     CK(g1_table.ensure((size_t)W * srs_n * sizeof(Affine<Fp>)));
     msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
         srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>());
@@ -1085,7 +1088,7 @@ struct Ctx final : kzg_gpu_ctx {
       if (is_inf) *is_inf = 1;
       return KZG_GPU_OK;
     }
-    if (!bytes || k > srs_n || k > (1ull << 22)) return KZG_GPU_ERR_ARG;
+    if (!bytes || k >= srs_n || k > (1ull << 22)) return KZG_GPU_ERR_ARG;  // create_commit: deg + 1 < _G1.size() (src/trusted_setup.cpp:138)
     CK(raw.ensure(byte_length));
     CK(stage.ensure(k * (size_t)SB));
     CK(cudaMemcpyAsync(raw.p, bytes, byte_length, cudaMemcpyHostToDevice, stream));

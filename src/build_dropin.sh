@@ -7,6 +7,7 @@
 #   oracle/_ref/dropin/benchmark-<curve>-gpu    benchmark/benchmark.cpp
 #   oracle/_ref/dropin/kzg-cli-bn254-gpu        demo/shared/kzg-cli.cpp (the demo's setup / commit / prove / verify CLI)
 #   oracle/_ref/dropin/kzgdrop-<curve>          oracle/ref_harness.cpp (same byte-file driver as kzgref-<curve>)
+#   oracle/_ref/dropin/dropin-threads-bn254     tests/cpp/dropin_threads.cpp (concurrent callers, cache eviction, copies)
 # Needs oracle/build_ref.sh to have run (MIRACL core.a, NTL ntl.a and generated headers in oracle/_ref/scratch).
 # Outputs are git-ignored and travel to the GPU box like the other built artefacts; /root/reference is
 # only needed here, at build time.
@@ -39,6 +40,7 @@ build_curve() {
   if [ "$c" = bn254 ]; then
     g++ -O2 $I "$REF/testing/testing.cpp" $L -o "$OUT/testing-bn254-gpu"
     g++ -O2 $I "$REF/demo/shared/kzg-cli.cpp" $L -o "$OUT/kzg-cli-bn254-gpu"
+    g++ -O2 -std=c++17 $I "$ROOT/tests/cpp/dropin_threads.cpp" $L -o "$OUT/dropin-threads-bn254"   # our own thread-safety test
     cp "$REF/testing/blob1.txt" "$REF/testing/blob2.txt" "$OUT/" 2>/dev/null || true
   fi
 }

@@ -19,11 +19,14 @@
 // a side table keyed by the object's address and validated by a fingerprint of its SRS.
 #include <kzg.h>
 
+#include <array>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <iostream>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -121,69 +124,156 @@ std::vector<uint8_t> pack_coeffs(const ZZ_pX& P) {
   return raw;
 }
 
-// ---- side table: trusted_setup object -> device context with its SRS resident
-struct DeviceSide {
-  kzg_gpu_ctx* ctx = nullptr;
+// ---- side table: trusted_setup object -> devices with its SRS resident
+//
+// kzg.h gives trusted_setup no spare member and no destructor, so the device side of a setup is found through two
+// maps under one mutex:
+//   by content   fingerprint of ALL its G1 and G2 bytes -> the resident copy (strong reference, least recently used
+//                of more than KZG_GPU_CACHE = 8 dropped): copies of a trusted_setup, and setups loaded twice from one
+//                file, share ONE resident SRS;
+//   by address   object address -> weak reference + a cheap stamp (size, first/last G1, second/last G2), so the
+//                common call does not re-serialise the SRS.
+// Callers receive a shared_ptr: a context that is evicted or replaced while another thread is inside a call on it
+// is destroyed only when that call returns.  Lookup, upload and insertion happen under the mutex, so two threads
+// making the first use of one setup upload it once.  Points are serialised from COPIES (ECP_toOctet normalises
+// its argument in place; the reference's readers never write to _G1/_G2 either).
+struct Side {
+  kzg_gpu_group* group = nullptr;
   size_t n = 0;
-  std::vector<uint8_t> stamp;  // first and last G1 point
+  ~Side() { if (group) kzg_gpu_group_destroy(group); }
+  kzg_gpu_ctx* ctx() const { return kzg_gpu_group_ctx(group, 0); }
+};
+using SidePtr = std::shared_ptr<Side>;
+using Digest = std::array<uint64_t, 2>;
+
+struct ByAddress {
+  std::weak_ptr<Side> side;
+  size_t n = 0;
+  std::vector<uint8_t> stamp;
+};
+struct ByContent {
+  SidePtr side;
   uint64_t age = 0;
 };
 std::mutex g_mu;
-std::map<const void*, DeviceSide> g_sides;
+std::map<const void*, ByAddress> g_by_address;
+std::map<Digest, ByContent> g_by_content;
 uint64_t g_clock = 0;
 
-std::vector<uint8_t> stamp_of(std::vector<ECP>& g1) {
-  std::vector<uint8_t> s(2 * G1_BYTES);
-  g1_body(g1.front(), s.data());
-  g1_body(g1.back(), s.data() + G1_BYTES);
+size_t cache_capacity() {
+  const char* e = getenv("KZG_GPU_CACHE");
+  const long v = e ? atol(e) : 0;
+  return v >= 1 ? (size_t)v : 8;
+}
+// how many devices a setup of n points is made resident on: all of them when a single commitment is large enough to be
+// split by point range (kzg_gpu_group_msm_g1), one otherwise; KZG_GPU_DEVICES overrides
+int devices_for(size_t n) {
+  const int visible = kzg_gpu_device_count();
+  if (visible <= 0) return 0;
+  const char* e = getenv("KZG_GPU_DEVICES");
+  if (e && atoi(e) >= 1) return std::min(atoi(e), visible);
+  return n >= 65536 ? visible : 1;
+}
+Digest digest_of(const std::vector<uint8_t>& b1, const std::vector<uint8_t>& b2) {
+  Digest d = {0xcbf29ce484222325ull, 0x84222325cbf29ce4ull};  // two FNV-1a style lanes over different strides
+  auto feed = [&](const std::vector<uint8_t>& v) {
+    for (size_t i = 0; i < v.size(); i++) {
+      d[0] = (d[0] ^ v[i]) * 0x100000001b3ull;
+      d[1] = (d[1] ^ (uint64_t)(v[i] + 0x9e) ^ (d[0] >> 29)) * 0x9e3779b97f4a7c15ull;
+    }
+  };
+  feed(b1);
+  feed(b2);
+  d[0] ^= b1.size();
+  d[1] ^= b2.size() * 0x9e3779b97f4a7c15ull;
+  return d;
+}
+std::vector<uint8_t> stamp_of(const std::vector<ECP>& g1, const std::vector<ECP2>& g2) {
+  std::vector<uint8_t> s(2 * G1_BYTES + 2 * G2_BYTES, 0);
+  ECP a = g1.front(), b = g1.back();  // copies: g1_body normalises in place
+  g1_body(a, s.data());
+  g1_body(b, s.data() + G1_BYTES);
+  if (!g2.empty()) {
+    ECP2 c = g2[g2.size() > 1 ? 1 : 0], d = g2.back();
+    g2_body(c, s.data() + 2 * G1_BYTES);
+    g2_body(d, s.data() + 2 * G1_BYTES + G2_BYTES);
+  }
   return s;
 }
-void evict_old_locked() {
-  while (g_sides.size() > 4) {
-    auto oldest = g_sides.begin();
-    for (auto it = g_sides.begin(); it != g_sides.end(); ++it)
+SidePtr new_side(size_t n) {
+  const int ndev = devices_for(n);
+  SidePtr side = std::make_shared<Side>();
+  int rc = ndev > 0 ? kzg_gpu_group_create(&side->group, CURVE_ID, nullptr, ndev) : KZG_GPU_ERR_CUDA;
+  if (rc) fail(nullptr, rc, "kzg_gpu_group_create (a CUDA device is required; there is no CPU fallback)");
+  side->n = n;
+  return side;
+}
+void remember_locked(const void* self, const SidePtr& side, const Digest& digest, std::vector<uint8_t> stamp) {
+  ByContent& c = g_by_content[digest];
+  c.side = side;
+  c.age = ++g_clock;
+  g_by_address[self] = ByAddress{side, side->n, std::move(stamp)};
+  const size_t cap = cache_capacity();
+  while (g_by_content.size() > cap) {  // drop the least recently used; in-flight callers keep theirs alive
+    auto oldest = g_by_content.begin();
+    for (auto it = g_by_content.begin(); it != g_by_content.end(); ++it)
       if (it->second.age < oldest->second.age) oldest = it;
-    kzg_gpu_ctx_destroy(oldest->second.ctx);
-    g_sides.erase(oldest);
+    g_by_content.erase(oldest);
   }
+  if (g_by_address.size() > 256)
+    for (auto it = g_by_address.begin(); it != g_by_address.end();)
+      it = it->second.side.expired() ? g_by_address.erase(it) : std::next(it);
 }
-kzg_gpu_ctx* new_ctx() {
-  kzg_gpu_ctx* ctx = nullptr;
-  int rc = kzg_gpu_ctx_create(&ctx, CURVE_ID, 0);
-  if (rc) fail(nullptr, rc, "kzg_gpu_ctx_create (a CUDA device is required; there is no CPU fallback)");
-  return ctx;
-}
-void remember(const void* self, kzg_gpu_ctx* ctx, std::vector<ECP>& g1) {
-  std::lock_guard<std::mutex> lock(g_mu);
-  auto it = g_sides.find(self);
-  if (it != g_sides.end()) kzg_gpu_ctx_destroy(it->second.ctx);
-  DeviceSide& d = g_sides[self];
-  d.ctx = ctx;
-  d.n = g1.size();
-  d.stamp = stamp_of(g1);
-  d.age = ++g_clock;
-  evict_old_locked();
-}
-// context of `self`, uploading the SRS the first time (or again if the object at this address changed)
-kzg_gpu_ctx* device_of(const void* self, std::vector<ECP>& g1, std::vector<ECP2>& g2) {
+// device side of `self`, uploading the SRS the first time (or again if the object at this address changed)
+SidePtr device_of(const void* self, const std::vector<ECP>& g1, const std::vector<ECP2>& g2) {
   if (g1.empty()) throw std::runtime_error("kzg gpu: empty trusted setup");
-  {
-    std::lock_guard<std::mutex> lock(g_mu);
-    auto it = g_sides.find(self);
-    if (it != g_sides.end() && it->second.n == g1.size() && it->second.stamp == stamp_of(g1)) {
-      it->second.age = ++g_clock;
-      return it->second.ctx;
+  std::lock_guard<std::mutex> lock(g_mu);
+  std::vector<uint8_t> stamp = stamp_of(g1, g2);
+  auto it = g_by_address.find(self);
+  if (it != g_by_address.end() && it->second.n == g1.size() && it->second.stamp == stamp) {
+    if (SidePtr side = it->second.side.lock()) {
+      for (auto& kv : g_by_content)
+        if (kv.second.side == side) kv.second.age = ++g_clock;
+      return side;
     }
   }
   const size_t n = g1.size();
   std::vector<uint8_t> b1(n * (size_t)G1_BYTES), b2(g2.size() == n ? n * (size_t)G2_BYTES : 0);
-  for (size_t i = 0; i < n; i++) g1_body(g1[i], b1.data() + i * G1_BYTES);
-  for (size_t i = 0; i < n && !b2.empty(); i++) g2_body(g2[i], b2.data() + i * G2_BYTES);
-  kzg_gpu_ctx* ctx = new_ctx();
-  int rc = kzg_gpu_srs_load(ctx, n, b1.data(), b2.empty() ? nullptr : b2.data());
-  if (rc) { std::string e = kzg_gpu_last_error(ctx); kzg_gpu_ctx_destroy(ctx); throw std::runtime_error("kzg gpu: srs_load failed " + e); }
-  remember(self, ctx, g1);
-  return ctx;
+  {
+    auto pack = [&](size_t lo, size_t hi) {
+      for (size_t i = lo; i < hi; i++) {
+        ECP p = g1[i];
+        g1_body(p, b1.data() + i * G1_BYTES);
+        if (!b2.empty()) {
+          ECP2 q = g2[i];
+          g2_body(q, b2.data() + i * G2_BYTES);
+        }
+      }
+    };
+    unsigned hw = std::thread::hardware_concurrency();
+    const size_t nt = n < 4096 ? 1 : std::min<size_t>(hw ? hw : 4, 16);
+    std::vector<std::thread> pool;
+    for (size_t t = 1; t < nt; t++) pool.emplace_back(pack, n * t / nt, n * (t + 1) / nt);
+    pack(0, n / nt);
+    for (auto& th : pool) th.join();
+  }
+  const Digest digest = digest_of(b1, b2);
+  auto hit = g_by_content.find(digest);
+  if (hit != g_by_content.end() && hit->second.side->n == n) {  // a copy of a setup that is already resident
+    SidePtr side = hit->second.side;
+    remember_locked(self, side, digest, std::move(stamp));
+    return side;
+  }
+  SidePtr side = new_side(n);
+  int rc = kzg_gpu_group_srs_load(side->group, n, b1.data(), b2.empty() ? nullptr : b2.data());
+  if (rc) throw std::runtime_error(std::string("kzg gpu: srs_load failed: ") + kzg_gpu_group_last_error(side->group));
+  remember_locked(self, side, digest, std::move(stamp));
+  return side;
+}
+
+void wipe(void* p, size_t len) {  // not elidable
+  volatile unsigned char* v = static_cast<volatile unsigned char*>(p);
+  for (size_t i = 0; i < len; i++) v[i] = 0;
 }
 
 }  // namespace
@@ -193,7 +283,10 @@ kzg_gpu_ctx* kzg_b200::poly_ctx() {
   static std::mutex mu;
   static kzg_gpu_ctx* ctx = nullptr;
   std::lock_guard<std::mutex> lock(mu);
-  if (!ctx) ctx = new_ctx();
+  if (!ctx) {
+    int rc = kzg_gpu_ctx_create(&ctx, CURVE_ID, 0);
+    if (rc) fail(nullptr, rc, "kzg_gpu_ctx_create (a CUDA device is required; there is no CPU fallback)");
+  }
   return ctx;
 }
 
@@ -245,26 +338,45 @@ void kzg::init() {  // same contract as the reference: NTL modulus = group order
 kzg::trusted_setup::trusted_setup(int num_coeff) {
   if (num_coeff < 2) throw invalid_argument("num_coeff must be at least 2");
   if (kzg::CURVE_ORDER_BYTES == 0) kzg::init();
-  BIG secret;
-  generate_random_BIG(secret);
   const int SB = kzg::CURVE_ORDER_BYTES;
-  std::vector<uint8_t> s_le(SB);
-  BytesFromZZ(s_le.data(), ZZ_from_BIG(secret), SB);
-
   const size_t n = (size_t)num_coeff;
   std::vector<uint8_t> b1(n * G1_BYTES), b2(n * G2_BYTES);
-  kzg_gpu_ctx* ctx = new_ctx();
-  int rc = kzg_gpu_setup_powers(ctx, s_le.data(), n, b1.data(), b2.data());
-  memset(s_le.data(), 0, s_le.size());
-  if (rc) { std::string e = kzg_gpu_last_error(ctx); kzg_gpu_ctx_destroy(ctx); throw std::runtime_error("kzg gpu: setup_powers failed " + e); }
+  SidePtr side = new_side(n);
+  int rc;
+  {
+    // The secret goes BIG -> big-endian bytes -> SB little-endian bytes without an NTL temporary, and both copies are
+    // wiped before anything else happens; the device scrubs its copy and the powers before setup_powers returns.
+    BIG secret;
+    generate_random_BIG(secret);
+    char be[MODBYTES_CURVE];
+    BIG_toBytes(be, secret);
+    uint8_t s_le[MODBYTES_CURVE];
+    for (int i = 0; i < SB; i++) s_le[i] = (uint8_t)be[MODBYTES_CURVE - 1 - i];
+    rc = kzg_gpu_group_setup_powers(side->group, s_le, n, b1.data(), b2.data());
+    wipe(secret, sizeof(secret));
+    wipe(be, sizeof(be));
+    wipe(s_le, sizeof(s_le));
+  }
+  if (rc) throw std::runtime_error(std::string("kzg gpu: setup_powers failed: ") + kzg_gpu_group_last_error(side->group));
   _G1.resize(n);
   _G2.resize(n);
-  for (size_t i = 0; i < n; i++) {
-    _G1[i] = g1_from_body(b1.data() + i * G1_BYTES, 0);
-    const bool checked = i < 2 || i + 1 == n || i == n / 2;
-    _G2[i] = checked ? g2_from_body(b2.data() + i * G2_BYTES, 0) : g2_from_device_body(b2.data() + i * G2_BYTES);
+  auto rebuild = [&](size_t lo, size_t hi) {
+    for (size_t i = lo; i < hi; i++) {
+      _G1[i] = g1_from_body(b1.data() + i * G1_BYTES, 0);
+      const bool checked = i < 2 || i + 1 == n || i == n / 2;
+      _G2[i] = checked ? g2_from_body(b2.data() + i * G2_BYTES, 0) : g2_from_device_body(b2.data() + i * G2_BYTES);
+    }
+  };
+  {
+    unsigned hw = std::thread::hardware_concurrency();
+    const size_t nt = n < 2048 ? 1 : std::min<size_t>(hw ? hw : 4, 16);
+    std::vector<std::thread> pool;
+    for (size_t t = 1; t < nt; t++) pool.emplace_back(rebuild, n * t / nt, n * (t + 1) / nt);
+    rebuild(0, n / nt);
+    for (auto& th : pool) th.join();
   }
-  remember(this, ctx, _G1);
+  std::lock_guard<std::mutex> lock(g_mu);
+  remember_locked(this, side, digest_of(b1, b2), stamp_of(_G1, _G2));
 }
 
 // trusted_setup(filename): same file format and the same three failure modes as src/trusted_setup.cpp:76-121.
@@ -312,18 +424,20 @@ void kzg::trusted_setup::generate_elements_range(int, int, const std::vector<BIG
 
 ECP kzg::trusted_setup::polyeval_G1(const ZZ_pX& P) {
   if (deg(P) == -1) return g1_from_body(nullptr, 1);
-  kzg_gpu_ctx* ctx = device_of(this, _G1, _G2);
+  SidePtr side = device_of(this, _G1, _G2);
   std::vector<uint8_t> raw = pack_coeffs(P);
   uint8_t xy[G1_BYTES];
   int is_inf = 0;
-  int rc = kzg_gpu_msm_g1(ctx, raw.data(), (uint64_t)(deg(P) + 1), 0, xy, &is_inf);
-  if (rc) fail(ctx, rc, "msm_g1");
+  // one device, or split by point range over all of them when the polynomial is large (kzg_gpu_group_msm_g1)
+  int rc = kzg_gpu_group_msm_g1(side->group, raw.data(), (uint64_t)(deg(P) + 1), 0, xy, &is_inf);
+  if (rc) throw std::runtime_error(std::string("kzg gpu: msm_g1: ") + kzg_gpu_group_last_error(side->group));
   return g1_from_body(xy, is_inf);
 }
 
 ECP2 kzg::trusted_setup::polyeval_G2(const ZZ_pX& P) {
   if (deg(P) == -1) return g2_from_body(nullptr, 1);
-  kzg_gpu_ctx* ctx = device_of(this, _G1, _G2);
+  SidePtr side = device_of(this, _G1, _G2);
+  kzg_gpu_ctx* ctx = side->ctx();
   std::vector<uint8_t> raw = pack_coeffs(P);
   uint8_t xy[G2_BYTES];
   int is_inf = 0;
@@ -356,7 +470,8 @@ kzg::proof kzg::trusted_setup::create_proof(const kzg::poly& poly, int chunk_off
   const ZZ_pX& P = poly.get_poly();
   const long n = deg(P) + 1;
   if (n <= chunk_length) return kzg::proof(g1_from_body(nullptr, 1));  // zero quotient
-  kzg_gpu_ctx* ctx = device_of(this, _G1, _G2);
+  SidePtr side = device_of(this, _G1, _G2);
+  kzg_gpu_ctx* ctx = side->ctx();
   std::vector<uint8_t> raw = pack_coeffs(P);
   uint8_t xy[G1_BYTES];
   int is_inf = 0;

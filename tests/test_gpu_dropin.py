@@ -41,6 +41,14 @@ def test_reference_test_program_on_gpu():
     assert plain.count("PASSED") == 36, plain
 
 
+def test_dropin_concurrent_callers_and_cache_eviction():
+    """tests/cpp/dropin_threads.cpp: 8 threads making the first use of one file-loaded setup, 11 live setups (more than
+    the resident-SRS cache holds) used from 4 threads, copies sharing one resident SRS."""
+    with tempfile.TemporaryDirectory() as td:
+        out = _run(_need(os.path.join(DROPIN, "dropin-threads-bn254")), os.path.join(td, "srs.bin"), cwd=DROPIN)
+    assert out.strip().startswith("OK"), out
+
+
 @pytest.mark.parametrize("cname", ["bn254", "bls12381"])
 def test_reference_benchmark_on_gpu(cname):
     """benchmark/benchmark.cpp, unmodified: every row verifies (BASELINE config 1 / 5 shapes, on the GPU path)."""
