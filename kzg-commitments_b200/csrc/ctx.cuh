@@ -112,12 +112,13 @@ struct kzg_gpu_ctx {
     coop_blocks[kernel] = v;
     return v;
   }
-  int launch_cooperative(const void* kernel, uint64_t blocks_wanted, int threads, void* args_struct) {
-    const int cap = max_cooperative_blocks(kernel, threads);
+  int launch_cooperative(const void* kernel, uint64_t blocks_wanted, int threads, void* args_struct, size_t smem = 0) {
+    int cap = max_cooperative_blocks(kernel, threads);
     if (cap <= 0) { last_error = "cooperative launch: kernel does not fit the device"; return KZG_GPU_ERR_CUDA; }
+    if (num_sms > 0) cap = std::min(cap, num_sms);  // one CTA per SM: cheap grid barriers, one warp per sub-partition
     const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(blocks_wanted, (uint64_t)cap));
     void* params[1] = {args_struct};
-    cudaError_t e = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3((unsigned)threads), params, 0, stream);
+    cudaError_t e = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3((unsigned)threads), params, smem, stream);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchCooperativeKernel");
     launches++;
     return KZG_GPU_OK;
@@ -178,7 +179,7 @@ struct Ctx final : kzg_gpu_ctx {
 
   ~Ctx() override {
     cudaSetDevice(device);
-    for (DevBuf* b : {&g1, &g2, &g1_table, &g2_table, &fb_sums, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
+    for (DevBuf* b : {&barrier_buf, &g1, &g2, &g1_table, &g2_table, &fb_sums, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
                       &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
       b->release();
@@ -336,10 +337,23 @@ struct Ctx final : kzg_gpu_ctx {
     return KZG_GPU_OK;
   }
 
-  // 4-lane teams of one msm_tail<F> launch at full cooperative size
+  // msm_tail<F>: one CTA of TAIL_THREADS per SM; the dynamic shared-memory request only keeps a second CTA off the SM
   template <class F>
-  uint64_t tail_teams() {
-    return (uint64_t)max_cooperative_blocks((const void*)msm_tail<F>, TAIL_THREADS) * (TAIL_THREADS / 4);
+  int prepare_tail() {
+    if (tail_ready[std::is_same<F, Fp2>::value ? 1 : 0]) return KZG_GPU_OK;
+    CK(cudaFuncSetAttribute(msm_tail<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
+    if (!barrier_buf.p) {
+      CK(barrier_buf.ensure(sizeof(GridBarrier)));
+      CK(cudaMemsetAsync(barrier_buf.p, 0, sizeof(GridBarrier), stream));
+    }
+    tail_ready[std::is_same<F, Fp2>::value ? 1 : 0] = true;
+    return KZG_GPU_OK;
+  }
+  bool tail_ready[2] = {false, false};
+  DevBuf barrier_buf;
+  uint64_t tail_threads_total() {
+    if (!num_sms) cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device);
+    return (uint64_t)(num_sms > 0 ? num_sms : 1) * TAIL_THREADS;
   }
 
   void phase_mark(int i) {
@@ -411,6 +425,10 @@ struct Ctx final : kzg_gpu_ctx {
     // Small and medium MSMs (and the narrow end of every large one) run their many short steps inside two
     // persistent cooperative kernels (msm_tail.cuh) instead of ~50 launches: "tail" option, on by default.
     const bool use_tail = opt_tail && opt_team;
+    if (use_tail) {
+      int rc0 = prepare_tail<F>();
+      if (rc0) return rc0;
+    }
     const bool fused_sort = use_tail && chunk_slices <= 1 && levels == 0 && records <= (1ull << 22) && nbuckets <= (1ull << 22);
     phase_mark(0);
     int rc = KZG_GPU_OK;
@@ -421,11 +439,11 @@ struct Ctx final : kzg_gpu_ctx {
       chunk_slices = 0;
       const uint64_t ntiles = (nbuckets + SCAN_TILE - 1) / SCAN_TILE;
       CK(tile_sums.ensure((ntiles + 1) * 4));
-      SortArgs sa{sh, d_scalars, digits.as<int32_t>(), ranks.as<uint32_t>(), counts.as<uint32_t>(), starts.as<uint32_t>(),
+      SortArgs sa{sh, barrier_buf.as<GridBarrier>(), d_scalars, digits.as<int32_t>(), ranks.as<uint32_t>(), counts.as<uint32_t>(), starts.as<uint32_t>(),
                   task_first.as<uint32_t>(), sorted.as<uint32_t>(), tile_sums.as<uint32_t>(), d_hist, d_hist_start,
                   d_hist_cursor, tasks.as<MsmTask>(), slot_seg.as<MsmSlotSeg>(), nbuckets, sh.chunk};
       const uint64_t want = (std::max<uint64_t>(records, nbuckets) + SCAN_THREADS - 1) / SCAN_THREADS;
-      rc = launch_cooperative((const void*)msm_sort_small<C>, want, SCAN_THREADS, &sa);
+      rc = launch_cooperative((const void*)msm_sort_small<C>, want, SCAN_THREADS, &sa);  // at most one CTA per SM
       if (rc) return rc;
     } else {
     CK(cudaMemsetAsync(counts.p, 0, (nbuckets + 1) * 4, stream));
@@ -502,9 +520,11 @@ struct Ctx final : kzg_gpu_ctx {
     // The reduction is a fixed sequence of steps whose item counts only shrink.  Steps wider than the tail
     // kernel's team count are machine-filling launches of their own; from the first step that fits, everything
     // that is left runs inside ONE cooperative kernel (msm_tail) with grid barriers between the steps.
-    const uint64_t tail_cap = use_tail ? 2 * tail_teams<F>() : 0;
-    const bool finish_in_tail = use_tail && batch <= 4096;  // one MSM per warp (see msm_tail)
+    // a step of up to four rounds of one group operation per thread (msm_tail.cuh) belongs in the tail
+    const uint64_t tail_cap = use_tail ? 4 * tail_threads_total() : 0;
+    const bool finish_in_tail = use_tail && batch <= tail_threads_total() / 32;  // one MSM per warp, one round (see msm_tail)
     TailArgs<F> ta{};
+    ta.barrier = barrier_buf.as<GridBarrier>();
     ta.ntasks_ptr = task_first.as<uint32_t>() + nbuckets;
     ta.max_nt = d_hist + MSM_MAX_CHUNK + 1;
     ta.slot_seg = slot_seg.as<MsmSlotSeg>();
@@ -519,9 +539,8 @@ struct Ctx final : kzg_gpu_ctx {
       ta.first_stage = first; ta.last_stage = last;
       ta.rin = rin; ta.rout = rout; ta.cin = cin; ta.cout = cout;
       ta.r_len = r_len; ta.c_len = c_len;
-      if (first <= TAIL_FOLD) items = std::max<uint64_t>(items, std::min<uint64_t>(max_tasks, tail_cap));
-      if (last >= TAIL_FINISH) items = std::max<uint64_t>(items, batch * 8);
-      return launch_cooperative((const void*)msm_tail<F>, (items * 4 + TAIL_THREADS - 1) / TAIL_THREADS, TAIL_THREADS, &ta);
+      (void)items;  // always one CTA per SM: narrow levels are dealt out one warp per SM first (msm_tail.cuh)
+      return launch_cooperative((const void*)msm_tail<F>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES);
     };
     const int tail_last = finish_in_tail ? TAIL_FINISH : TAIL_COMBINE;
     bool in_tail = false;

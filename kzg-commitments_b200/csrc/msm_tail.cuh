@@ -3,31 +3,89 @@
 // A small or medium MSM (one create_commit of degree 4096, the per-GPU share of a point-range split) spends most
 // of its time in steps that cannot fill the machine: a dozen sort/scan launches of a few microseconds each in
 // front of the bucket accumulation and ~35 reduction launches behind it (round 1: 2^12 points = 0.60 ms of which
-// 0.05 ms accumulate; profiles/r1k_curves_and_sizes.md).  Every one of those launches paid a launch gap, a cold
-// instruction cache for a different kernel body and an L2 round trip.  Here each end is ONE kernel whose CTAs are
-// all resident (cudaLaunchCooperativeKernel) and which walks through the same steps separated by grid barriers:
+// 0.05 ms accumulate; profiles/r1k_curves_and_sizes.md).  Here each end is ONE kernel with exactly one CTA per SM
+// (cudaLaunchCooperativeKernel: all resident) that walks through the same steps separated by grid barriers:
 //
 //   msm_sort_small   zero -> digits + histogram -> bucket offsets (3-phase scan) -> scatter -> tasks per bucket
 //                    (scan) -> task-length histogram -> its scan -> task placement            (was 13 launches)
 //   msm_tail         fold of task partials -> 2-D bucket reduction (row / column trees, weighted chunks, trees)
 //                    -> group combine -> Horner over windows, affine normalisation, bytes     (was up to ~40 launches)
 //
-// msm_tail takes a [first_stage, last_stage] range: reduction levels that are still wider than the kernel's team
-// count stay separate, machine-filling launches (msm_bucket_pairs / msm_pair_sum in msm.cuh), issued between a
-// fold-only call and the call that finishes the narrow levels.  All group operations run on the 4-lane teams of
-// msm_team.cuh.  Data passes between steps through global memory; cooperative_groups' grid.sync() provides the
-// barrier and the fences that make one CTA's stores visible to the others' loads.
+// What bounds these steps (measured, profiles/r2a_*): ONE warp's Montgomery product already saturates its SM
+// sub-partition's multiplier pipe (an IMAD.WIDE issues every 4 cycles per SMSP), so a dependent chain of group
+// operations runs at full speed only with one warp per sub-partition; a second warp on the same sub-partition
+// halves both.  The first version of this kernel packed the items of a narrow level into the first few CTAs
+// (4 warps per sub-partition) and was SLOWER than the launches it replaced.  Hence the layout here:
+//   * 148 CTAs x 128 threads, one CTA per SM (a large dynamic shared-memory request keeps a second one away),
+//     i.e. exactly one warp per sub-partition;
+//   * items are dealt out warp-major ACROSS the CTAs: a level of <= 1184 items keeps one warp per SM busy,
+//     <= 4736 items one warp per sub-partition (4-lane teams, msm_team.cuh: 8 group operations per warp);
+//   * levels wider than two such rounds run one group operation per THREAD instead (14 dependent products, but
+//     32 per warp), which is the machine-filling form; still wider levels stay separate launches (ctx.cuh).
+// msm_tail takes a [first_stage, last_stage] range so that ctx.cuh can place the wide launches between a
+// fold-only call and the call that finishes the narrow levels.  Data passes between steps through global memory.
+// The grid barrier is a generation counter in device memory: one atomic per CTA to arrive, the last arrival bumps
+// the generation, the others poll it with ld.acquire and a short sleep (148 pollers hammering one L2 line was the
+// other thing that made the first version slow); __threadfence on both sides gives the usual grid.sync() ordering
+// and invalidates the SM's L1 before data written by other CTAs is read.
 #pragma once
 #include "msm_team.cuh"
 
 #if defined(__CUDACC__)
-#include <cooperative_groups.h>
 
 namespace kzgb200 {
 
-namespace cg = cooperative_groups;
+constexpr int TAIL_THREADS = 128;          // one warp per SM sub-partition
+constexpr int TAIL_SMEM_BYTES = 120 << 10; // dynamic shared memory requested only to keep the CTA alone on its SM
 
-constexpr int TAIL_THREADS = 256;  // 64 teams per CTA
+struct GridBarrier {        // lives in device memory, zero-initialised once; reusable across launches
+  unsigned count;
+  unsigned pad0[31];
+  unsigned gen;
+  unsigned pad1[31];
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// all CTAs of the (cooperatively launched) grid
+__device__ __forceinline__ void grid_sync(GridBarrier* b) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned g = ld_acquire_u32(&b->gen);  // cannot change before this CTA has arrived
+    __threadfence();
+    if (atomicAdd(&b->count, 1u) == gridDim.x - 1) {
+      atomicExch(&b->count, 0u);
+      __threadfence();
+      atomicAdd(&b->gen, 1u);
+    } else {
+      while (ld_acquire_u32(&b->gen) == g) __nanosleep(64);
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// Item distribution: virtual warp v = warp-in-CTA * gridDim + CTA, so consecutive groups of items land on
+// different SMs first and on a second warp of the same SM only after every SM has one.
+struct TailLane {
+  uint64_t vwarp, nvwarps;
+  int lane;
+  __device__ __forceinline__ TailLane() {
+    lane = threadIdx.x & 31;
+    vwarp = (uint64_t)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    nvwarps = (uint64_t)(blockDim.x >> 5) * gridDim.x;
+  }
+  __device__ __forceinline__ uint64_t team() const { return vwarp * 8 + (lane >> 2); }
+  __device__ __forceinline__ uint64_t nteams() const { return nvwarps * 8; }
+  __device__ __forceinline__ uint64_t thread() const { return vwarp * 32 + lane; }
+  __device__ __forceinline__ uint64_t nthreads() const { return nvwarps * 32; }
+  // a level of `items` group operations runs on teams while that takes at most two rounds
+  __device__ __forceinline__ bool use_teams(uint64_t items) const { return items <= 2 * nteams(); }
+};
 
 enum TailStage : int {
   TAIL_FOLD = 0, TAIL_BUCKET_PAIRS = 1, TAIL_TREES1 = 2, TAIL_WEIGHTED = 3, TAIL_TREES2 = 4, TAIL_COMBINE = 5, TAIL_FINISH = 6
@@ -36,6 +94,7 @@ enum TailStage : int {
 template <class F>
 struct TailArgs {
   int first_stage, last_stage;
+  GridBarrier* barrier;
   // fold
   const uint32_t* ntasks_ptr;
   const uint32_t* max_nt;
@@ -61,132 +120,177 @@ struct TailArgs {
 
 // one level of two pairwise trees side by side: out[i] = in[2i] + in[2i+1]
 template <class F>
-__device__ __forceinline__ void tail_pair_level(const XYZZ<F>* in0, XYZZ<F>* out0, uint64_t n0, const XYZZ<F>* in1,
-                                                XYZZ<F>* out1, uint64_t n1, uint64_t team, uint64_t nteams) {
-  for (uint64_t t = team; t < n0 + n1; t += nteams) {
-    const bool second = t >= n0;
-    const uint64_t i = second ? t - n0 : t;
-    const XYZZ<F>* in = second ? in1 : in0;
-    const XYZZ<F> a = in[2 * i], b = in[2 * i + 1];
-    const XYZZ<F> s = team_add<F>(a, b);
-    if ((threadIdx.x & 3) == 0) (second ? out1 : out0)[i] = s;
+__device__ __forceinline__ void tail_pair_level(const TailLane& tl, const XYZZ<F>* in0, XYZZ<F>* out0, uint64_t n0,
+                                                const XYZZ<F>* in1, XYZZ<F>* out1, uint64_t n1) {
+  if (tl.use_teams(n0 + n1)) {
+    for (uint64_t t = tl.team(); t < n0 + n1; t += tl.nteams()) {
+      const bool second = t >= n0;
+      const uint64_t i = second ? t - n0 : t;
+      const XYZZ<F>* in = second ? in1 : in0;
+      const XYZZ<F> a = in[2 * i], b = in[2 * i + 1];
+      const XYZZ<F> s = team_add<F>(a, b);
+      if ((threadIdx.x & 3) == 0) (second ? out1 : out0)[i] = s;
+    }
+  } else {
+    for (uint64_t t = tl.thread(); t < n0 + n1; t += tl.nthreads()) {
+      const bool second = t >= n0;
+      const uint64_t i = second ? t - n0 : t;
+      const XYZZ<F>* in = second ? in1 : in0;
+      XYZZ<F> acc = in[2 * i];
+      acc.add(in[2 * i + 1]);
+      (second ? out1 : out0)[i] = acc;
+    }
   }
 }
 
 // halve both trees until one value per sum is left; a grid barrier after every level
 template <class F>
-__device__ __forceinline__ void tail_trees(cg::grid_group& grid, XYZZ<F>*& in0, XYZZ<F>*& out0, uint64_t sums0, uint64_t& len0,
-                                           XYZZ<F>*& in1, XYZZ<F>*& out1, uint64_t sums1, uint64_t& len1, uint64_t team,
-                                           uint64_t nteams) {
+__device__ __forceinline__ void tail_trees(const TailLane& tl, GridBarrier* bar, XYZZ<F>*& in0, XYZZ<F>*& out0, uint64_t sums0,
+                                           uint64_t& len0, XYZZ<F>*& in1, XYZZ<F>*& out1, uint64_t sums1, uint64_t& len1) {
   while (len0 > 1 || len1 > 1) {
-    tail_pair_level<F>(in0, out0, len0 > 1 ? sums0 * (len0 / 2) : 0, in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0, team, nteams);
+    tail_pair_level<F>(tl, in0, out0, len0 > 1 ? sums0 * (len0 / 2) : 0, in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0);
     if (len0 > 1) { XYZZ<F>* t = in0; in0 = out0; out0 = t; len0 /= 2; }
     if (len1 > 1) { XYZZ<F>* t = in1; in1 = out1; out1 = t; len1 /= 2; }
-    grid.sync();
+    grid_sync(bar);
   }
 }
 
 template <class F>
-__global__ void __launch_bounds__(TAIL_THREADS, sizeof(F) <= 48 ? 2 : 1) msm_tail(TailArgs<F> a) {
-  cg::grid_group grid = cg::this_grid();
-  const uint64_t team = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 2;
-  const uint64_t nteams = ((uint64_t)gridDim.x * blockDim.x) >> 2;
+__global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
+  const TailLane tl;
   const bool lead = (threadIdx.x & 3) == 0;
   XYZZ<F>*rin = a.rin, *rout = a.rout, *cin = a.cin, *cout = a.cout;
   uint64_t r_len = a.r_len, c_len = a.c_len;
 
   if (a.first_stage <= TAIL_FOLD && a.last_stage >= TAIL_FOLD) {
-    // segmented binary tree over the task partials of each bucket (msm_fold_level_team), all levels in one launch
+    // Segmented binary tree over the task partials of each bucket (msm_fold_level_team), all levels in one launch.
+    // A warp scans 32 consecutive slots at a time (coalesced) and its teams then take the few that have work.
     const uint32_t max_nt = *a.max_nt, ntasks = *a.ntasks_ptr;
     for (uint32_t stride = 1; stride < max_nt; stride <<= 1) {
-      for (uint64_t q = team; q < ntasks; q += nteams) {
-        const MsmSlotSeg sg = a.slot_seg[q];
-        if ((sg.k & (2u * stride - 1u)) == 0u && sg.k + stride < sg.nt) {
-          const XYZZ<F> x = a.partial[q], y = a.partial[q + stride];
-          const XYZZ<F> s = team_add<F>(x, y);
-          __syncwarp(Team().mask);  // every lane has read partial[q] before the leader overwrites it
-          if (lead) a.partial[q] = s;
+      for (uint64_t q0 = tl.vwarp * 32; q0 < ntasks; q0 += tl.nvwarps * 32) {
+        const uint64_t q = q0 + tl.lane;
+        bool work = false;
+        if (q < ntasks) {
+          const MsmSlotSeg sg = a.slot_seg[q];
+          work = (sg.k & (2u * stride - 1u)) == 0u && sg.k + stride < sg.nt;
+        }
+        unsigned pending = __ballot_sync(0xffffffffu, work);
+        while (pending) {  // eight at a time, one per team
+          const int my = tl.lane >> 2;
+          unsigned m = pending;
+          int pick = -1;
+          for (int k = 0; k <= my && m; k++) {  // the (my+1)-th set bit
+            pick = __ffs(m) - 1;
+            m &= m - 1;
+            if (k < my) pick = -1;
+          }
+          if (pick >= 0) {
+            const uint64_t qq = q0 + pick;
+            const XYZZ<F> x = a.partial[qq], y = a.partial[qq + stride];
+            const XYZZ<F> s = team_add<F>(x, y);
+            __syncwarp(Team().mask);  // every lane has read partial[qq] before the leader overwrites it
+            if (lead) a.partial[qq] = s;
+          }
+          for (int k = 0; k < 8 && pending; k++) pending &= pending - 1;  // drop the eight that were taken
         }
       }
-      grid.sync();
+      grid_sync(a.barrier);
     }
   }
   if (a.first_stage <= TAIL_BUCKET_PAIRS && a.last_stage >= TAIL_BUCKET_PAIRS) {
-    // level 0 of the row and column trees, reading bucket values through task_first (msm_bucket_pairs_team)
+    // level 0 of the row and column trees, reading bucket values through task_first (msm_bucket_pairs)
     const uint64_t Lr = a.Cn >= 2 ? a.Cn / 2 : 1, Lc = a.R >= 2 ? a.R / 2 : 1;
     const BucketJob<F> jr{rin, a.R, a.Cn, a.Cn, 1, a.groups * a.R * Lr};
     const BucketJob<F> jc{cin, a.Cn, a.R, 1, a.Cn, a.groups * a.Cn * Lc};
-    for (uint64_t t0 = team; t0 < jr.total + jc.total; t0 += nteams) {
-      const bool second = t0 >= jr.total;
-      const BucketJob<F>& jb = second ? jc : jr;
-      const uint64_t t = second ? t0 - jr.total : t0;
-      const uint64_t P = jb.len >= 2 ? jb.len / 2 : 1;
-      const uint64_t p = t % P, gs = t / P;
-      const uint64_t s = gs % jb.nsums, g = gs / jb.nsums;
-      const uint64_t b0 = g * a.nb + s * jb.sstride + 2 * p * jb.jstride;
-      XYZZ<F> acc = bucket_value<F>(a.task_first, a.partial, b0);
-      if (jb.len >= 2) acc = team_add<F>(acc, bucket_value<F>(a.task_first, a.partial, b0 + jb.jstride));
-      if (lead) jb.out[t] = acc;
+    const uint64_t total = jr.total + jc.total;
+    if (tl.use_teams(total)) {
+      for (uint64_t t0 = tl.team(); t0 < total; t0 += tl.nteams()) {
+        const bool second = t0 >= jr.total;
+        const BucketJob<F>& jb = second ? jc : jr;
+        const uint64_t t = second ? t0 - jr.total : t0;
+        const uint64_t P = jb.len >= 2 ? jb.len / 2 : 1;
+        const uint64_t p = t % P, gs = t / P;
+        const uint64_t s = gs % jb.nsums, g = gs / jb.nsums;
+        const uint64_t b0 = g * a.nb + s * jb.sstride + 2 * p * jb.jstride;
+        XYZZ<F> acc = bucket_value<F>(a.task_first, a.partial, b0);
+        if (jb.len >= 2) acc = team_add<F>(acc, bucket_value<F>(a.task_first, a.partial, b0 + jb.jstride));
+        if (lead) jb.out[t] = acc;
+      }
+    } else {
+      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+        const bool second = t0 >= jr.total;
+        msm_bucket_pair_thread<F>(second ? jc : jr, a.nb, a.task_first, a.partial, second ? t0 - jr.total : t0);
+      }
     }
     r_len = Lr;
     c_len = Lc;
-    grid.sync();
+    grid_sync(a.barrier);
   }
   if (a.first_stage <= TAIL_TREES1 && a.last_stage >= TAIL_TREES1)
-    tail_trees<F>(grid, rin, rout, a.groups * a.R, r_len, cin, cout, a.groups * a.Cn, c_len, team, nteams);
+    tail_trees<F>(tl, a.barrier, rin, rout, a.groups * a.R, r_len, cin, cout, a.groups * a.Cn, c_len);
   if (a.first_stage <= TAIL_WEIGHTED && a.last_stage >= TAIL_WEIGHTED) {
-    // rin = row sums [groups * R], cin = column sums [groups * Cn]: weighted chunks (msm_weighted_chunks_team)
+    // rin = row sums [groups * R], cin = column sums [groups * Cn]: weighted chunks (msm_weighted_chunks)
     const uint64_t Pr = a.R >= WCHUNK ? a.R / WCHUNK : 1, Pc = a.Cn >= WCHUNK ? a.Cn / WCHUNK : 1;
-    const uint64_t total_r = a.groups * Pr, total_c = a.groups * Pc;
-    for (uint64_t t0 = team; t0 < total_r + total_c; t0 += nteams) {
-      const bool second = t0 >= total_r;
-      const uint64_t t = second ? t0 - total_r : t0;
-      const uint64_t m = second ? a.Cn : a.R;
-      const XYZZ<F>* in = second ? cin : rin;
-      const uint32_t woff = second ? 1u : 0u;
-      const uint64_t P = m >= WCHUNK ? m / WCHUNK : 1;
-      const uint64_t p = t % P, g = t / P;
-      const uint64_t j0i = p * WCHUNK, j1i = (j0i + WCHUNK < m) ? j0i + WCHUNK : m;
-      XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
-      for (uint64_t j = j1i; j > j0i; j--) {
-        const XYZZ<F> v = in[g * m + j - 1];
-        run = team_add<F>(run, v);
-        acc = team_add<F>(acc, run);
+    const WeightedJob<F> wr{rin, rout, a.R, a.groups * Pr, 0u};
+    const WeightedJob<F> wc{cin, cout, a.Cn, a.groups * Pc, 1u};
+    const uint64_t total = wr.total + wc.total;
+    if (tl.use_teams(total)) {
+      for (uint64_t t0 = tl.team(); t0 < total; t0 += tl.nteams()) {
+        const bool second = t0 >= wr.total;
+        const WeightedJob<F>& jb = second ? wc : wr;
+        const uint64_t t = second ? t0 - wr.total : t0;
+        const uint64_t m = jb.m;
+        const uint64_t P = m >= WCHUNK ? m / WCHUNK : 1;
+        const uint64_t p = t % P, g = t / P;
+        const uint64_t j0i = p * WCHUNK, j1i = (j0i + WCHUNK < m) ? j0i + WCHUNK : m;
+        XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
+        for (uint64_t j = j1i; j > j0i; j--) {
+          const XYZZ<F> v = jb.in[g * m + j - 1];
+          run = team_add<F>(run, v);
+          acc = team_add<F>(acc, run);
+        }
+        const uint32_t k = (uint32_t)j0i + jb.woff;
+        if (k >= 1) acc = team_add<F>(acc, team_small_mul<F>(run, k - 1));
+        else {
+          run.negate();
+          acc = team_add<F>(acc, run);
+        }
+        if (lead) jb.out[t] = acc;
       }
-      const uint32_t k = (uint32_t)j0i + woff;
-      if (k >= 1) acc = team_add<F>(acc, team_small_mul<F>(run, k - 1));
-      else {
-        run.negate();
-        acc = team_add<F>(acc, run);
+    } else {
+      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+        const bool second = t0 >= wr.total;
+        msm_weighted_chunk_thread<F>(second ? wc : wr, second ? t0 - wr.total : t0);
       }
-      if (lead) (second ? cout : rout)[t] = acc;
     }
     { XYZZ<F>* t = rin; rin = rout; rout = t; }
     { XYZZ<F>* t = cin; cin = cout; cout = t; }
     r_len = Pr;
     c_len = Pc;
-    grid.sync();
+    grid_sync(a.barrier);
   }
   if (a.first_stage <= TAIL_TREES2 && a.last_stage >= TAIL_TREES2)
-    tail_trees<F>(grid, rin, rout, a.groups, r_len, cin, cout, a.groups, c_len, team, nteams);
+    tail_trees<F>(tl, a.barrier, rin, rout, a.groups, r_len, cin, cout, a.groups, c_len);
   if (a.first_stage <= TAIL_COMBINE && a.last_stage >= TAIL_COMBINE) {
     // group_out[g] = 2^h * T1[g] + T2[g]
-    for (uint64_t g = team; g < a.groups; g += nteams) {
-      XYZZ<F> acc = rin[g];
-      for (int k = 0; k < a.h; k++) acc = team_dbl<F>(acc);
-      const XYZZ<F> b = cin[g];
-      acc = team_add<F>(acc, b);
-      if (lead) a.group_out[g] = acc;
+    if (tl.use_teams(a.groups)) {
+      for (uint64_t g = tl.team(); g < a.groups; g += tl.nteams()) {
+        XYZZ<F> acc = rin[g];
+        for (int k = 0; k < a.h; k++) acc = team_dbl<F>(acc);
+        const XYZZ<F> b = cin[g];
+        acc = team_add<F>(acc, b);
+        if (lead) a.group_out[g] = acc;
+      }
+    } else {
+      for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads()) msm_group_combine_thread<F>(a.h, rin, cin, a.group_out, g);
     }
-    if (a.last_stage >= TAIL_FINISH) grid.sync();
+    if (a.last_stage >= TAIL_FINISH) grid_sync(a.barrier);
   }
   if (a.first_stage <= TAIL_FINISH && a.last_stage >= TAIL_FINISH) {
     // one MSM per WARP (its first team): the inversion behind to_affine is a data-dependent loop, and different
     // inversions in one warp would serialise
-    const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
-    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    if ((threadIdx.x & 31) < 4) {
-      for (uint64_t m = warp; m < a.batch; m += nwarps) {
+    if (tl.lane < 4) {
+      for (uint64_t m = tl.vwarp; m < a.batch; m += tl.nvwarps) {
         XYZZ<F> acc = a.group_out[m * a.groups_per_msm + (a.groups_per_msm - 1)];
         for (int g = a.groups_per_msm - 2; g >= 0; g--) {
           for (int k = 0; k < a.c; k++) acc = team_dbl<F>(acc);
@@ -215,6 +319,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, sizeof(F) <= 48 ? 2 : 1) msm_tai
 // The sort end: scalars -> signed digits -> records grouped by bucket -> tasks ordered by length, one launch.
 struct SortArgs {
   MsmShape sh;
+  GridBarrier* barrier;
   const uint8_t* scalars;
   int32_t* digits;
   uint32_t* ranks;
@@ -232,36 +337,35 @@ struct SortArgs {
   int task_chunk;        // records per task (the scan divides by it)
 };
 
-static __device__ __forceinline__ void sort_scan(cg::grid_group& grid, uint64_t n, int chunk, const uint32_t* in,
-                                                 uint32_t* tile_sums, uint32_t* out) {
+static __device__ __forceinline__ void sort_scan(GridBarrier* bar, uint64_t n, int chunk, const uint32_t* in, uint32_t* tile_sums,
+                                                 uint32_t* out) {
   const uint64_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
   for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) scan_tile_sum_body(n, chunk, in, tile_sums, tile);
-  grid.sync();
+  grid_sync(bar);
   if (blockIdx.x == 0) scan_tiles_body(ntiles, tile_sums);
-  grid.sync();
+  grid_sync(bar);
   for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
     scan_apply_body(n, chunk, in, tile_sums, out, nullptr, tile, ntiles);
-  grid.sync();
+  grid_sync(bar);
 }
 
 template <class C>
 __global__ void __launch_bounds__(SCAN_THREADS) msm_sort_small(SortArgs a) {
-  cg::grid_group grid = cg::this_grid();
   const uint64_t gtid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x, gsize = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = gtid; i <= a.nbuckets; i += gsize) a.counts[i] = 0;
   for (uint64_t i = gtid; i < MSM_MAX_CHUNK + 2; i += gsize) a.hist[i] = 0;
-  grid.sync();
+  grid_sync(a.barrier);
   const uint64_t total = a.sh.n * a.sh.batch;
   for (uint64_t t = gtid; t < total; t += gsize) msm_digits_thread<C>(a.sh, a.scalars, a.digits, a.ranks, a.counts, t);
-  grid.sync();
-  sort_scan(grid, a.nbuckets, 0, a.counts, a.tile_sums, a.starts);
+  grid_sync(a.barrier);
+  sort_scan(a.barrier, a.nbuckets, 0, a.counts, a.tile_sums, a.starts);
   const uint64_t records = total * (uint64_t)a.sh.W;
   for (uint64_t t = gtid; t < records; t += gsize) msm_scatter_thread(a.sh, a.digits, a.starts, a.ranks, a.sorted, t);
-  sort_scan(grid, a.nbuckets, a.task_chunk, a.counts, a.tile_sums, a.task_first);
+  sort_scan(a.barrier, a.nbuckets, a.task_chunk, a.counts, a.tile_sums, a.task_first);
   msm_task_hist_body(a.nbuckets, a.task_chunk, a.starts, a.task_first, a.hist);
-  grid.sync();
+  grid_sync(a.barrier);
   msm_task_hist_scan_body(a.hist, a.hist_start, a.hist_cursor);
-  grid.sync();
+  grid_sync(a.barrier);
   msm_task_place_body(a.nbuckets, a.task_chunk, a.starts, a.task_first, a.hist_start, a.hist_cursor, a.tasks, a.slot_seg);
 }
 
