@@ -252,16 +252,24 @@ struct Ctx final : kzg_gpu_ctx {
     msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
         srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>());
     LAUNCHED();
-    if (have_g2 && opt_precompute >= 2) {
-      CK(g2_table.ensure((size_t)W * srs_n * sizeof(Affine<Fp2>)));
-      msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, stream>>>(
-          srs_n, srs_n, c, W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>());
-      LAUNCHED();
-    }
     CK(cudaStreamSynchronize(stream));
     table_c = c;
     table_W = W;
     return reserve_scratch();
+  }
+  // The G2 window table is built LAZILY, by the first G2 MSM of at least G2_TABLE_MIN_TERMS terms: G2 MSMs only carry the
+  // k + 1 coefficients of a vanishing polynomial (verify_proof, src/trusted_setup.cpp:241), a setup that is never
+  // asked for a many-point verification never pays for the table (it was most of trusted_setup(4096) through the
+  // drop-in in round 1: 36 ms on BLS12-381), and it is not built at all for SRS sizes where it would take gigabytes.
+  static constexpr uint64_t G2_TABLE_MIN_TERMS = 256;
+  int ensure_g2_table(uint64_t count) {
+    if (g2_table.p || !have_g2 || opt_precompute < 2 || !table_c || count < G2_TABLE_MIN_TERMS) return KZG_GPU_OK;
+    if ((double)table_W * (double)srs_n * sizeof(Affine<Fp2>) > 8e9) return KZG_GPU_OK;
+    CK(g2_table.ensure((size_t)table_W * srs_n * sizeof(Affine<Fp2>)));
+    msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, stream>>>(
+        srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>());
+    LAUNCHED();
+    return KZG_GPU_OK;
   }
 
   // Size the MSM scratch for one MSM over the whole SRS now, so that the first commitment of each new size does
@@ -274,7 +282,7 @@ struct Ctx final : kzg_gpu_ctx {
     int rc = enqueue_msm<Fp>(g1.as<Affine<Fp>>(), g1_table.p ? g1_table.as<Affine<Fp>>() : nullptr, table_c, nullptr, cnt, 1, 0, true);
     if (rc) return rc;
     if (have_g2 && srs_n <= (1ull << 16))  // verify-side MSMs (k + 1 terms)
-      rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), g2_table.p ? g2_table.as<Affine<Fp2>>() : nullptr, table_c, nullptr, cnt, 1, 0, true);
+      rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), table_c ? g2.as<Affine<Fp2>>() : nullptr, table_c, nullptr, cnt, 1, 0, true);
     return rc;
   }
 
@@ -687,6 +695,10 @@ struct Ctx final : kzg_gpu_ctx {
     if ((count && !scalars) || batch == 0) return KZG_GPU_ERR_ARG;
     if (base_offset + count > srs_n || base_offset + count < count) return KZG_GPU_ERR_ARG;
     last_group = group;
+    if (group == 2) {
+      int rc0 = ensure_g2_table(count);
+      if (rc0) return rc0;
+    }
     const int nco = group == 2 ? 4 : 2;
     if (count == 0) {  // empty sum = infinity (polyeval_G1 on the zero polynomial, src/trusted_setup.cpp:150-154)
       if (do_fetch) {
@@ -1142,11 +1154,17 @@ struct Ctx final : kzg_gpu_ctx {
         gen2.x.a.v[i] = C::g2xa(i); gen2.x.b.v[i] = C::g2xb(i);
         gen2.y.a.v[i] = C::g2ya(i); gen2.y.b.v[i] = C::g2yb(i);
       }
-      const unsigned grid = (W * FB_HALF + 63) / 64;
-      fixed_base_table<C, Fp><<<grid, 64, 0, stream>>>(gen1, t1);
+      fixed_base_rows<C, Fp><<<(4 * W + 127) / 128, 128, 0, stream>>>(gen1, t1);
       LAUNCHED();
-      fixed_base_table<C, Fp2><<<grid, 64, 0, stream>>>(gen2, t2);
+      fixed_base_rows<C, Fp2><<<(4 * W + 127) / 128, 128, 0, stream>>>(gen2, t2);
       LAUNCHED();
+      for (int level = 0; level + 1 < FB_C; level++) {
+        const unsigned grid = (unsigned)(((uint64_t)W << level) + 127) / 128;
+        fixed_base_fill<C, Fp><<<grid, 128, 0, stream>>>(level, t1);
+        LAUNCHED();
+        fixed_base_fill<C, Fp2><<<grid, 128, 0, stream>>>(level, t2);
+        LAUNCHED();
+      }
       e = cudaStreamSynchronize(stream);
       if (e == cudaSuccess) e = cudaGetLastError();
       if (e != cudaSuccess) { cudaFree(t1); cudaFree(t2); CK(e); }

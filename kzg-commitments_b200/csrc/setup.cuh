@@ -3,17 +3,19 @@
 //   trusted_setup::generate_elements_range       src/trusted_setup.cpp:123-135
 // (n independent NTL power() calls, then one PAIR_G1mul and one PAIR_G2mul per index spread over
 // std::threads).  Here: s^i by chunked running products, then a fixed-base comb — a table
-// T[w][d-1] = d * 2^(8w) * G (d = 1..128, affine) built once per context, 8-bit signed digits,
-// one mixed add per window, one inversion per output point.
+// T[w][d-1] = d * 2^(16w) * G (d = 1..32768, affine) built once per process and device, 16-bit signed
+// digits, one mixed add per window (16 per index for the 254/255-bit orders; round 1 used 8-bit windows = 32
+// adds per index and spent 53 ms on 2^20 indices, profiles/r1o_setup.md), one inversion per 8 output points.
 // Also: the per-SRS precomputed window table used by the MSM (msm.cuh).
 #pragma once
 #include "msm.cuh"
+#include "msm_team.cuh"
 #include "poly.cuh"
 
 namespace kzgb200 {
 
-constexpr int FB_C = 8;                       // fixed-base window bits
-constexpr int FB_HALF = 1 << (FB_C - 1);      // 128 table entries per window
+constexpr int FB_C = 16;                      // fixed-base window bits
+constexpr int FB_HALF = 1 << (FB_C - 1);      // 32768 table entries per window (G1 + G2, BLS12-381: 16 x 32768 x 288 B = 151 MB)
 
 template <class C>
 KZG_HD constexpr int fb_windows() { return (C::SCALAR_BITS + 1 + FB_C - 1) / FB_C; }
@@ -48,22 +50,37 @@ __global__ void setup_powers_kernel(uint64_t n, uint64_t first_index, const uint
   }
 }
 
-// table[w * 128 + (d-1)] = d * 2^(8w) * G    (one thread per entry; context-creation time only)
+// table[w * FB_HALF + (d-1)] = d * 2^(FB_C w) * G, built in FB_C launches:
+//   fixed_base_rows   B_w = 2^(FB_C w) G for every window: one 4-lane team per window runs its chain of doublings
+//                     (three product rounds per doubling instead of nine on one thread; the longest chain, 240
+//                     doublings, is the latency of the whole build);
+//   fixed_base_fill   level j = 0 .. FB_C-2 doubles the filled prefix of every row: (2^j + r) B = 2^j B + r B for
+//                     r = 1 .. 2^j, one affine + affine addition and one inversion per new entry (r = 2^j is the
+//                     doubling, which the mixed addition's P + P branch takes).
+// Round 1 ran a full double-and-add scalar multiplication per entry (~2400 products each); this is ~25.
+#if defined(__CUDACC__)
 template <class C, class F>
-__global__ void fixed_base_table(Affine<F> gen, Affine<F>* __restrict__ table) {
+__global__ void fixed_base_rows(Affine<F> gen, Affine<F>* __restrict__ table) {
   constexpr int W = fb_windows<C>();
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= W * FB_HALF) return;
-  const int w = t / FB_HALF, d = (t % FB_HALF) + 1;
-  constexpr int KW = (W * FB_C + FB_C + 31) / 32 + 1;
-  uint32_t k[KW];
-  for (int i = 0; i < KW; i++) k[i] = 0;
-  const int pos = w * FB_C;
-  k[pos >> 5] |= (uint32_t)d << (pos & 31);
-  if ((pos & 31) + 8 > 32) k[(pos >> 5) + 1] |= (uint32_t)d >> (32 - (pos & 31));
-  XYZZ<F> r = scalar_mul_bits<F>(gen, k, pos + FB_C);
-  table[t] = r.to_affine();
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 2;
+  if (w >= W) return;  // whole teams leave together
+  XYZZ<F> acc = XYZZ<F>::from_affine(gen);
+  for (int i = 0; i < w * FB_C; i++) acc = team_dbl<F>(acc);
+  if ((threadIdx.x & 3) == 0) table[(size_t)w * FB_HALF] = acc.to_affine();
 }
+template <class C, class F>
+__global__ void __launch_bounds__(128) fixed_base_fill(int level, Affine<F>* __restrict__ table) {
+  constexpr int W = fb_windows<C>();
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t per = 1u << level;
+  if (t >= (uint32_t)W * per) return;
+  const uint32_t w = t >> level, r = (t & (per - 1u)) + 1u;  // new multiple d = 2^level + r
+  Affine<F>* row = table + (size_t)w * FB_HALF;
+  XYZZ<F> acc = XYZZ<F>::from_affine(row[per - 1]);
+  acc.madd(row[r - 1], false);
+  row[per + r - 1] = acc.to_affine();
+}
+#endif
 
 // sums[i] = powers[i] * G in XYZZ coordinates (normalised afterwards by fixed_base_to_affine: a per-thread
 // inversion here is a divergent binary-GCD loop that costs a warp about as much as its 33 mixed additions,
