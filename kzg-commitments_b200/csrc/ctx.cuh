@@ -876,8 +876,36 @@ struct Ctx final : kzg_gpu_ctx {
     const Fr* q;
     // measured on B200 at degree 4095 (tools/gpu_probe_quotient.py): the scan kernel costs 0.08 ms per root, the
     // power-series path 0.69 ms whatever k is -> series from 8 roots on
-    const bool series = batch == 1 && !d_roots && opt_long_division >= 3 && k >= 8 && k <= 16384 && n - k <= 16384;
-    if (k < 48 && !series) {  // a few opened points: one CTA-wide suffix scan per root
+    // One polynomial: pick the cheapest of  k rounds on one CTA (~70 us + 1.4 ns per coefficient, per root),
+    // k rounds over the whole GPU (~55 us + 0.02 ns per coefficient, per root: long polynomials, few roots) and the
+    // power-series path (~0.3 ms + L^2 / 42 us for L = n - k quotient coefficients, whatever k is), from the timings
+    // of tools/gpu_probe_quotient.py.  Batches keep one CTA per polynomial (the batch fills the machine).
+    const uint64_t Lq = n - k;
+    const bool single = batch == 1 && !d_roots;
+    const double cost_cta = (double)k * (70.0 + (double)n * 1.4e-3);
+    const double cost_grid = single && n >= 32768 ? (double)k * (55.0 + (double)n * 2e-5) : 1e300;
+    const double cost_series = single && opt_long_division >= 3 && k >= 8 && k <= 65536 && Lq <= 65536
+                                   ? 300.0 + (double)Lq * (double)Lq / 42e3 : 1e300;
+    const bool series = cost_series < cost_cta && cost_series < cost_grid;
+    const bool rounds_grid = !series && cost_grid < cost_cta && opt_long_division >= 3;
+    if (rounds_grid) {
+      if (!barrier_buf.p) {
+        CK(barrier_buf.ensure(sizeof(GridBarrier)));
+        CK(cudaMemsetAsync(barrier_buf.p, 0, sizeof(GridBarrier), stream));
+      }
+      constexpr int QG = 256;
+      CK(tile_sums.ensure(2 * 1024 * sizeof(Fr)));
+      struct { uint64_t n; long long first_root; uint64_t k; Fr* b0; Fr* b1; Fr* agg; GridBarrier* bar; } qa{
+          n, (long long)first_root, k, poly0.as<Fr>(), poly1.as<Fr>(), tile_sums.as<Fr>(), barrier_buf.as<GridBarrier>()};
+      void* params[7] = {&qa.n, &qa.first_root, &qa.k, &qa.b0, &qa.b1, &qa.agg, &qa.bar};
+      const void* kern = (const void*)poly_quotient_rounds_grid<C, QG>;
+      int cap = max_cooperative_blocks(kern, QG);
+      if (cap <= 0) { last_error = "cooperative launch: kernel does not fit the device"; return KZG_GPU_ERR_CUDA; }
+      cap = std::min(std::min(cap, num_sms > 0 ? num_sms : cap), QG);
+      CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)cap), dim3(QG), params, 0, stream));
+      launches++;
+      q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
+    } else if ((k < 48 || (single && opt_long_division >= 3)) && !series) {  // one CTA-wide suffix scan per root
       constexpr int QT = 512;
       poly_quotient_rounds<C, QT><<<(unsigned)batch, QT, 0, stream>>>(n, (long long)first_root, d_roots, k, poly0.as<Fr>(),
                                                                       poly1.as<Fr>());

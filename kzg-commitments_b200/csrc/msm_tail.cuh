@@ -29,6 +29,7 @@
 // other thing that made the first version slow); __threadfence on both sides gives the usual grid.sync() ordering
 // and invalidates the SM's L1 before data written by other CTAs is read.
 #pragma once
+#include "grid_barrier.cuh"
 #include "msm_team.cuh"
 
 #if defined(__CUDACC__)
@@ -37,37 +38,6 @@ namespace kzgb200 {
 
 constexpr int TAIL_THREADS = 128;          // one warp per SM sub-partition
 constexpr int TAIL_SMEM_BYTES = 120 << 10; // dynamic shared memory requested only to keep the CTA alone on its SM
-
-struct GridBarrier {        // lives in device memory, zero-initialised once; reusable across launches
-  unsigned count;
-  unsigned pad0[31];
-  unsigned gen;
-  unsigned pad1[31];
-};
-
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
-// all CTAs of the (cooperatively launched) grid
-__device__ __forceinline__ void grid_sync(GridBarrier* b) {
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned g = ld_acquire_u32(&b->gen);  // cannot change before this CTA has arrived
-    __threadfence();
-    if (atomicAdd(&b->count, 1u) == gridDim.x - 1) {
-      atomicExch(&b->count, 0u);
-      __threadfence();
-      atomicAdd(&b->gen, 1u);
-    } else {
-      while (ld_acquire_u32(&b->gen) == g) __nanosleep(64);
-    }
-    __threadfence();
-  }
-  __syncthreads();
-}
 
 // Item distribution: virtual warp v = warp-in-CTA * gridDim + CTA, so consecutive groups of items land on
 // different SMs first and on a second warp of the same SM only after every SM has one.

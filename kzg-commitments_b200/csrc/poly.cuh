@@ -15,6 +15,7 @@
 #include <cooperative_groups.h>
 #endif
 #include "field.cuh"
+#include "grid_barrier.cuh"
 
 namespace kzgb200 {
 
@@ -136,6 +137,82 @@ poly_quotient_rounds(uint64_t n, long long first_root, const long long* __restri
       c = Fr::add(Fr::mul(c, a), src[j - 1]);               // r[j-1]
     }
     __syncthreads();
+    Fr* t = src; src = dst; dst = t;
+    m -= 1;
+  }
+}
+
+// ---------------------------------------------------------------- the same k rounds over the WHOLE GPU
+// One polynomial that is too long for one CTA (the reference's large-degree path, benchmark/benchmark.cpp:123-136:
+// degrees up to 8 388 608, where a single CTA would walk 2^23 coefficients per root): a cooperative launch, one CTA
+// per SM, every thread owns a contiguous segment.  Per root: segment Horner sums, a suffix scan of the affine maps
+// c -> h + a^len c first inside each CTA and then (redundantly in every CTA, through shared memory) over the CTA
+// aggregates, a grid barrier, the second sweep over the segment that writes the quotient, a grid barrier.
+// The barrier is grid_barrier.cuh's generation counter.
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+poly_quotient_rounds_grid(uint64_t n, long long first_root, uint64_t k, Field<typename C::FrP>* buf0,
+                          Field<typename C::FrP>* buf1, Field<typename C::FrP>* agg /* 2 * gridDim */, GridBarrier* bar) {
+  using Fr = Field<typename C::FrP>;
+  __shared__ Fr s_val[THREADS];
+  __shared__ Fr s_mul[THREADS];
+  const int tid = threadIdx.x;
+  const uint64_t T = (uint64_t)gridDim.x * THREADS, gt = (uint64_t)blockIdx.x * THREADS + tid;
+  Fr* src = buf0;
+  Fr* dst = buf1;
+  uint64_t m = n;
+  for (uint64_t round = 0; round < k; round++) {
+    const Fr a = fr_from_i64<C>(first_root + (long long)round);
+    const uint64_t seg = (m + T - 1) / T;
+    const uint64_t lo = min(seg * gt, m), hi = min(lo + seg, m);
+    Fr h = Fr::zero();
+    for (uint64_t j = hi; j > lo; j--) h = Fr::add(Fr::mul(h, a), src[j - 1]);
+    s_val[tid] = h;
+    s_mul[tid] = fr_pow_u32<Fr>(a, (uint32_t)(hi - lo));
+    __syncthreads();
+    for (int d = 1; d < THREADS; d <<= 1) {  // suffix scan inside the CTA (as poly_quotient_rounds)
+      Fr v = s_val[tid], mu = s_mul[tid];
+      Fr v2 = Fr::zero(), mu2 = Fr::one();
+      const bool has = tid + d < THREADS;
+      if (has) { v2 = s_val[tid + d]; mu2 = s_mul[tid + d]; }
+      __syncthreads();
+      if (has) {
+        s_val[tid] = Fr::add(v, Fr::mul(mu, v2));
+        s_mul[tid] = Fr::mul(mu, mu2);
+      }
+      __syncthreads();
+    }
+    // carry into this thread's segment from the REST OF THIS CTA (as if nothing lay above the CTA), and the map of
+    // the segments between this thread and the top of the CTA
+    const Fr c_local = (tid + 1 < THREADS) ? s_val[tid + 1] : Fr::zero();
+    const Fr mul_above = (tid + 1 < THREADS) ? s_mul[tid + 1] : Fr::one();
+    if (tid == 0) { agg[2 * blockIdx.x] = s_val[0]; agg[2 * blockIdx.x + 1] = s_mul[0]; }
+    grid_sync(bar);
+    // carry into this CTA: suffix scan over the aggregates of the CTAs above (gridDim <= THREADS)
+    __syncthreads();
+    if (tid < (int)gridDim.x) { s_val[tid] = agg[2 * tid]; s_mul[tid] = agg[2 * tid + 1]; }
+    else { s_val[tid] = Fr::zero(); s_mul[tid] = Fr::one(); }
+    __syncthreads();
+    for (int d = 1; d < (int)gridDim.x; d <<= 1) {
+      Fr v = s_val[tid], mu = s_mul[tid];
+      Fr v2 = Fr::zero(), mu2 = Fr::one();
+      const bool has = tid + d < THREADS;
+      if (has) { v2 = s_val[tid + d]; mu2 = s_mul[tid + d]; }
+      __syncthreads();
+      if (has) {
+        s_val[tid] = Fr::add(v, Fr::mul(mu, v2));
+        s_mul[tid] = Fr::mul(mu, mu2);
+      }
+      __syncthreads();
+    }
+    const Fr c_cta = (blockIdx.x + 1 < gridDim.x) ? s_val[blockIdx.x + 1] : Fr::zero();
+    __syncthreads();
+    Fr c = Fr::add(c_local, Fr::mul(mul_above, c_cta));  // r[hi] of this thread's segment
+    for (uint64_t j = hi; j > lo; j--) {
+      if (j - 1 < m - 1) dst[j - 1] = c;       // q[j-1] = r[j]   (q has m-1 coefficients)
+      c = Fr::add(Fr::mul(c, a), src[j - 1]);  // r[j-1]
+    }
+    grid_sync(bar);
     Fr* t = src; src = dst; dst = t;
     m -= 1;
   }

@@ -171,3 +171,42 @@ def test_two_ranks_nccl_fold_matches_oracle():
     assert line["n_gpus"] == 2 and line["parity_asserted"] is True
     assert line["strong"]["msm_2p17"]["parity_asserted"] and line["commit"]["parity_asserted"]
     assert line["commit"]["blobs"] == 65
+
+
+def test_quotient_paths_for_long_polynomials():
+    """Large-degree polynomials (the reference's --benchmark-common path, benchmark/benchmark.cpp:123-136): k rounds over
+    the whole GPU for long polynomials with few roots, the power-series path beyond the round-1 cap of 16384 quotient
+    coefficients; checked against the oracle's synthetic division and against the independent systolic kernel."""
+    cname = "bn254"
+    C = get_curve(cname)
+    ctx = kzg_b200.Context(cname, 0)
+    rng = random.Random(31)
+    n = (1 << 17) + 3
+    P = [rng.randrange(C.r) for _ in range(n)]
+    raw = C.scalars_to_bytes(P)
+    for off, k in ((5, 1), (123456789, 3)):
+        q = list(P)
+        for j in range(k):  # k synthetic divisions by (x - (off + j))
+            a = (off + j) % C.r
+            out = [0] * (len(q) - 1)
+            carry = 0
+            for i in range(len(q) - 1, 0, -1):
+                carry = (q[i] + carry * a) % C.r
+                out[i - 1] = carry
+            q = out
+        assert ctx.poly_quotient(raw, off, k) == C.scalars_to_bytes(q), (off, k)
+    # proof over the long polynomial: quotient (grid rounds) + MSM of 2^17 + 2 terms
+    s = rng.randrange(C.r)
+    ctx.set_option("setup_g2", 0)
+    ctx.setup_powers(s, n, want_bytes=False)
+    xy, inf = ctx.prove(raw, 5, 1)
+    qs = (C.poly_eval(P, s) - C.poly_eval(P, 5)) * pow(s - 5, -1, C.r) % C.r
+    assert xy == C.g1_to_octet(C.mul(qs, C.g1))[1:]
+    # many roots, quotient longer than 16384 coefficients: series path == systolic path
+    n2, k2 = 40000, 18000
+    raw2 = C.scalars_to_bytes([rng.randrange(C.r) for _ in range(n2)])
+    q_series = ctx.poly_quotient(raw2, 7, k2)
+    ctx.set_option("long_division", 0)
+    assert ctx.poly_quotient(raw2, 7, k2) == q_series
+    ctx.set_option("long_division", 3)
+    ctx.close()
