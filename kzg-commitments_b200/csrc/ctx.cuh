@@ -72,7 +72,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1, opt_table_pad = 0;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -159,6 +159,7 @@ struct Ctx final : kzg_gpu_ctx {
   DevBuf g1, g2;             // Affine<Fp>[n], Affine<Fp2>[n]
   DevBuf g1_table, g2_table; // per-SRS window tables T[w][i] = 2^(c*w) * G_i (row 0 = the SRS itself)
   int table_c = 0, table_W = 0;
+  size_t g1_point_stride = sizeof(Affine<Fp>);
   // fixed-base tables of the generators
   // (constants of the curve: built once per process and device, shared by every context, never freed)
   struct FbShared { Affine<Fp>* t1 = nullptr; Affine<Fp2>* t2 = nullptr; };
@@ -248,9 +249,11 @@ struct Ctx final : kzg_gpu_ctx {
       last_error = "window_bits is too small for the per-SRS window table (more than 40 windows); use precompute = 0 with it";
       return KZG_GPU_ERR_ARG;
     }
-    CK(g1_table.ensure((size_t)W * srs_n * sizeof(Affine<Fp>)));
+    // "table_pad" experiment: one 128-byte line per 96-byte point (BLS12-381), so a gathered point never straddles two lines
+    g1_point_stride = opt_table_pad && sizeof(Affine<Fp>) <= 128 ? 128 : sizeof(Affine<Fp>);
+    CK(g1_table.ensure((size_t)W * srs_n * g1_point_stride));
     msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
-        srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>());
+        srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>(), g1_point_stride);
     LAUNCHED();
     CK(cudaStreamSynchronize(stream));
     table_c = c;
@@ -267,7 +270,7 @@ struct Ctx final : kzg_gpu_ctx {
     if ((double)table_W * (double)srs_n * sizeof(Affine<Fp2>) > 8e9) return KZG_GPU_OK;
     CK(g2_table.ensure((size_t)table_W * srs_n * sizeof(Affine<Fp2>)));
     msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, stream>>>(
-        srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>());
+        srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>(), sizeof(Affine<Fp2>));
     LAUNCHED();
     return KZG_GPU_OK;
   }
@@ -392,6 +395,7 @@ struct Ctx final : kzg_gpu_ctx {
     // by random-gather bandwidth, while the XYZZ kernel hides one gather behind 10 modmuls.
     int levels = 0;
     if (std::is_same<F, Fp>::value) levels = opt_affine_levels >= 0 ? opt_affine_levels : 0;
+    if (g1_point_stride != sizeof(Affine<Fp>)) levels = 0;  // the affine levels read the table at its natural stride
     sh.chunk = opt_task_chunk ? std::min(opt_task_chunk, MSM_MAX_CHUNK)
                               : (int)std::min<uint64_t>(128, std::max<uint64_t>(4, (records >> levels) / 65536));
     if (records >= (1ull << 31) || (precomp && (uint64_t)sh.W * srs_n >= (1ull << 31))) return KZG_GPU_ERR_ARG;
@@ -517,8 +521,9 @@ struct Ctx final : kzg_gpu_ctx {
     phase_mark(1);
     {
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)1 << 30);
+      const size_t pt_stride = (precomp && std::is_same<F, Fp>::value && levels == 0) ? g1_point_stride : sizeof(Affine<F>);
       msm_accumulate<F><<<grid, 128, 0, stream>>>(task_first.as<uint32_t>() + nbuckets, tasks.as<MsmTask>(), seg_sorted,
-                                                  seg_pts, partial.as<XYZZ<F>>());
+                                                  seg_pts, partial.as<XYZZ<F>>(), pt_stride);
       LAUNCHED();
     }
     phase_mark(2);

@@ -305,14 +305,17 @@ KZG_HD void msm_task_place_thread(int chunk, const uint32_t* starts, const uint3
     slot_seg[t.slot] = MsmSlotSeg{k, nt};
   }
 }
+// point_stride: bytes from one source point to the next (sizeof(Affine<F>), or 128 for the padded window table of
+// the "table_pad" experiment, profiles/r2_gather_layout.md)
 template <class F>
 KZG_HD void msm_accumulate_thread(const MsmTask* tasks, const uint32_t* sorted, const Affine<F>* bases,
-                                  XYZZ<F>* partial, uint32_t i) {
+                                  XYZZ<F>* partial, uint32_t i, size_t point_stride = sizeof(Affine<F>)) {
   const MsmTask t = tasks[i];
   XYZZ<F> acc = XYZZ<F>::inf();
+  const char* base_bytes = reinterpret_cast<const char*>(bases);
   for (uint32_t e = t.first; e < t.first + t.len; e++) {
     const uint32_t rec = sorted ? sorted[e] : e;  // no record array: the points were pre-reduced (msm_affine.cuh)
-    const Affine<F> p = bases[rec & 0x7fffffffu];
+    const Affine<F> p = *reinterpret_cast<const Affine<F>*>(base_bytes + (size_t)(rec & 0x7fffffffu) * point_stride);
     acc.madd(p, (rec >> 31) != 0);
   }
   partial[t.slot] = acc;
@@ -400,10 +403,11 @@ msm_task_place(uint64_t nbuckets, int chunk, const uint32_t* __restrict__ starts
 template <class F>
 __global__ void __launch_bounds__(128, sizeof(F) <= 48 ? 4 : 1)
 msm_accumulate(const uint32_t* __restrict__ ntasks_ptr, const MsmTask* __restrict__ tasks,
-               const uint32_t* __restrict__ sorted, const Affine<F>* __restrict__ bases, XYZZ<F>* __restrict__ partial) {
+               const uint32_t* __restrict__ sorted, const Affine<F>* __restrict__ bases, XYZZ<F>* __restrict__ partial,
+               size_t point_stride) {
   const uint32_t ntasks = *ntasks_ptr;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ntasks; i += gridDim.x * blockDim.x)
-    msm_accumulate_thread<F>(tasks, sorted, bases, partial, i);
+    msm_accumulate_thread<F>(tasks, sorted, bases, partial, i, point_stride);
 }
 // Device fold: a segmented binary tree over the flat array of task partials, one launch per level.
 // At level l the partial of task k (k a multiple of 2^(l+1)) absorbs that of task k + 2^l of the same

@@ -157,9 +157,14 @@ fixed_base_to_affine(uint64_t n, const XYZZ<F>* __restrict__ sums, Affine<F>* __
 template <class F, int MAXW>
 __global__ void __launch_bounds__(128)
 msm_precompute_table(uint64_t n, uint64_t stride, int c, int W, const Affine<F>* __restrict__ base,
-                     Affine<F>* __restrict__ table) {
+                     Affine<F>* __restrict__ table_ptr, size_t point_stride) {
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
+  // entries lie point_stride bytes apart (sizeof(Affine<F>) normally; 128 in the padded-table experiment)
+  struct Strided {
+    char* p; size_t st;
+    __device__ Affine<F>& operator[](uint64_t k) const { return *reinterpret_cast<Affine<F>*>(p + k * st); }
+  } table{reinterpret_cast<char*>(table_ptr), point_stride};
   const Affine<F> p0 = base[i];
   table[i] = p0;
   if (p0.is_inf()) {
