@@ -180,6 +180,8 @@ struct Ctx final : kzg_gpu_ctx {
 
   ~Ctx() override {
     cudaSetDevice(device);
+    if (aux_stream) { cudaStreamSynchronize(aux_stream); cudaStreamDestroy(aux_stream); }
+    if (g2_table_ev) cudaEventDestroy(g2_table_ev);
     for (DevBuf* b : {&barrier_buf, &g1, &g2, &g1_table, &g2_table, &fb_sums, &nt_g0, &nt_g1, &nt_u, &raw, &stage, &scal2, &scal, &digits, &counts, &starts, &task_first,
                       &cursor, &sorted, &partial, &group_out, &out_bytes, &out_inf, &out_xyzz, &poly0, &poly1,
                       &qbytes, &powers, &tile_sums, &hist, &tasks, &slot_seg, &ranks, &aff_off, &aff_a, &aff_b, &aff_prefix, &aff_totals, &roots, &inv_fact, &it_u, &it_pa, &it_pb, &it_za, &it_zb, &red0, &red1, &red2, &red3})
@@ -238,6 +240,8 @@ struct Ctx final : kzg_gpu_ctx {
     return best;
   }
   int build_table() {
+    if (aux_stream) CK(cudaStreamSynchronize(aux_stream));  // a table build of the previous SRS may still be running
+    g2_table_pending = false;
     g1_table.release();
     g2_table.release();
     table_c = table_W = 0;
@@ -264,14 +268,35 @@ struct Ctx final : kzg_gpu_ctx {
   // k + 1 coefficients of a vanishing polynomial (verify_proof, src/trusted_setup.cpp:241), a setup that is never
   // asked for a many-point verification never pays for the table (it was most of trusted_setup(4096) through the
   // drop-in in round 1: 36 ms on BLS12-381), and it is not built at all for SRS sizes where it would take gigabytes.
+  // For the SRS sizes the reference's callers use (<= 65536 points) the build starts when the SRS becomes resident, on a
+  // SIDE stream, so that neither the constructor nor the commitments that follow wait for it; the first G2 MSM does.
   static constexpr uint64_t G2_TABLE_MIN_TERMS = 256;
-  int ensure_g2_table(uint64_t count) {
-    if (g2_table.p || !have_g2 || opt_precompute < 2 || !table_c || count < G2_TABLE_MIN_TERMS) return KZG_GPU_OK;
+  static constexpr uint64_t G2_TABLE_EAGER_MAX_SRS = 65536;
+  cudaStream_t aux_stream = nullptr;
+  cudaEvent_t g2_table_ev = nullptr;
+  bool g2_table_pending = false;
+  int ensure_g2_table(uint64_t count, bool eager = false) {
+    if (g2_table.p || !have_g2 || opt_precompute < 2 || !table_c) return KZG_GPU_OK;
+    if (!eager && count < G2_TABLE_MIN_TERMS) return KZG_GPU_OK;
+    if (eager && srs_n > G2_TABLE_EAGER_MAX_SRS) return KZG_GPU_OK;
     if ((double)table_W * (double)srs_n * sizeof(Affine<Fp2>) > 8e9) return KZG_GPU_OK;
     CK(g2_table.ensure((size_t)table_W * srs_n * sizeof(Affine<Fp2>)));
-    msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, stream>>>(
+    if (!aux_stream) CK(cudaStreamCreateWithFlags(&aux_stream, cudaStreamNonBlocking));
+    if (!g2_table_ev) CK(cudaEventCreateWithFlags(&g2_table_ev, cudaEventDisableTiming));
+    CK(cudaEventRecord(g2_table_ev, stream));          // the SRS itself was written on the main stream
+    CK(cudaStreamWaitEvent(aux_stream, g2_table_ev, 0));
+    msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, aux_stream>>>(
         srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>(), sizeof(Affine<Fp2>));
     LAUNCHED();
+    CK(cudaEventRecord(g2_table_ev, aux_stream));
+    g2_table_pending = true;
+    return KZG_GPU_OK;
+  }
+  int wait_g2_table() {  // before the main stream reads (or frees) the table
+    if (g2_table_pending) {
+      CK(cudaStreamWaitEvent(stream, g2_table_ev, 0));
+      g2_table_pending = false;
+    }
     return KZG_GPU_OK;
   }
 
@@ -286,7 +311,28 @@ struct Ctx final : kzg_gpu_ctx {
     if (rc) return rc;
     if (have_g2 && srs_n <= (1ull << 16))  // verify-side MSMs (k + 1 terms)
       rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), table_c ? g2.as<Affine<Fp2>>() : nullptr, table_c, nullptr, cnt, 1, 0, true);
-    return rc;
+    if (rc) return rc;
+    return warm_up();
+  }
+  // One two-term MSM of zero scalars per group right after the SRS became resident: the first launch of every kernel of
+  // the pipeline loads its code (CUDA loads modules lazily) and sets its attributes here instead of inside the first
+  // create_commit (round 1: the first commitment of a process took 1.0 ms against 0.5 ms for the second).  Then the
+  // G2 window table starts building on the side stream, and the 1/t! table of the interpolation on the main one.
+  int warm_up() {
+    const uint64_t cnt = std::min<uint64_t>(2, srs_n);
+    CK(scal.ensure(cnt * (size_t)SB));
+    CK(cudaMemsetAsync(scal.p, 0, cnt * (size_t)SB, stream));
+    int rc = enqueue_msm<Fp>(g1.as<Affine<Fp>>(), g1_table.p ? g1_table.as<Affine<Fp>>() : nullptr, table_c, scal.as<uint8_t>(), cnt, 1, 0);
+    if (!rc && have_g2) rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), nullptr, table_c, scal.as<uint8_t>(), cnt, 1, 0);
+    if (rc) return rc;
+    last_batch = 0;
+    if (inv_fact_n < 4096 && srs_n <= G2_TABLE_EAGER_MAX_SRS) {
+      CK(inv_fact.ensure(4096 * sizeof(Fr)));
+      fr_inv_factorials<C><<<1, 32, 0, stream>>>(4096u, inv_fact.as<Fr>());
+      LAUNCHED();
+      inv_fact_n = 4096;
+    }
+    return ensure_g2_table(0, /*eager=*/true);
   }
 
   int srs_load(uint64_t n, const uint8_t* h_g1, const uint8_t* h_g2) override {
@@ -702,6 +748,7 @@ struct Ctx final : kzg_gpu_ctx {
     last_group = group;
     if (group == 2) {
       int rc0 = ensure_g2_table(count);
+      if (!rc0) rc0 = wait_g2_table();
       if (rc0) return rc0;
     }
     const int nco = group == 2 ? 4 : 2;
@@ -1078,7 +1125,7 @@ struct Ctx final : kzg_gpu_ctx {
   int enqueue_interpolate(int64_t first_x, uint64_t k, Fr** p_out, Fr** z_out, bool with_p = true) {
     uint64_t kp = 1;
     while (kp < k) kp <<= 1;
-    if (inv_fact_n < k) {  // 1/t! table, cached
+    if (with_p && inv_fact_n < k) {  // 1/t! table (only the interpolant needs it), cached
       const uint64_t want = std::max<uint64_t>(kp, 4096);
       CK(inv_fact.ensure(want * sizeof(Fr)));
       fr_inv_factorials<C><<<1, 32, 0, stream>>>((uint32_t)want, inv_fact.as<Fr>());

@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--precompute", default="0")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--team", default="1")
+    ap.add_argument("--table-pad", type=int, default=0)
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     ctx = kzg_b200.Context(args.curve, 0)
@@ -44,6 +45,7 @@ def main():
     stream = torch.cuda.ExternalStream(ctx.stream)
     ctx.set_option("setup_g2", 0)
     ctx.set_option("profile", 1)
+    ctx.set_option("table_pad", args.table_pad)
     for lg in [int(x) for x in args.sizes.split(",")]:
         n = 1 << lg
         sc = torch.from_numpy(random_scalars(n, lg, ctx.r, ctx.SB).reshape(-1)).cuda()
