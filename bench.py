@@ -623,6 +623,64 @@ def run_secondary(kzg_b200, np, torch, local):
     return out
 
 
+def run_single_process(args):
+    """--single-process: ONE process drives --gpus N devices through the kzg_gpu_group C ABI (include/kzg_gpu.h
+    "Multi-GPU": one context + one host worker thread per device) instead of one process per GPU over NCCL.  Prints one
+    JSON line of the same shape; value = points/s of ONE 2^log2n-point MSM from pinned host memory, split by point
+    range over the devices (strong scaling), plus the 4096-blob commit / proof batch sharded by blob.  Results are
+    asserted byte-identical to a one-device group."""
+    import numpy as np
+    import torch
+    import kzg_b200
+    n, G = 1 << args.log2n, args.gpus
+    big = torch.from_numpy(random_scalars(n, 0x4B5A47).view(np.uint8).reshape(-1)).pin_memory()
+    nc, nb = 4096, max(args.blobs, 1)
+    blobs = torch.from_numpy(random_scalars(nb * nc, 77).view(np.uint8).reshape(-1)).pin_memory()
+    roots = [i % 4096 for i in range(nb)]
+
+    def measure(g):
+        grp = kzg_b200.Group(CURVE, g)
+        grp.set_option("setup_g2", 0)
+        grp.setup_powers(SECRET, n, want_bytes=False)
+        for _ in range(max(args.warmup, 3)):
+            grp.msm_g1(big, n)
+        ts = []
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            xy = grp.msm_g1(big, n)
+            ts.append((time.perf_counter() - t0) * 1e3)
+        grp.setup_powers(SECRET, nc + 1, want_bytes=False)
+        grp.msm_g1_batch(blobs, nc, nb)
+        t0 = time.perf_counter()
+        cm = grp.msm_g1_batch(blobs, nc, nb)
+        t_c = (time.perf_counter() - t0) * 1e3
+        grp.prove_batch(blobs, nc, roots, 1)
+        t0 = time.perf_counter()
+        pr = grp.prove_batch(blobs, nc, roots, 1)
+        t_p = (time.perf_counter() - t0) * 1e3
+        grp.close()
+        return sum(ts) / len(ts), xy, t_c, cm, t_p, pr
+
+    ms1, xy1, c1, cm1, p1, pr1 = measure(1)
+    msG, xyG, cG, cmG, pG, prG = measure(G) if G > 1 else (ms1, xy1, c1, cm1, p1, pr1)
+    assert xy1 == xyG and cm1 == cmG and pr1 == prG, "group results differ from the single-device results"
+    line = {"metric": "g1_msm_points_per_s", "value": n / (msG * 1e-3), "unit": "points/s", "n_gpus": G, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": msG, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u32 limbs (Montgomery, 12x32-bit Fp / 8x32-bit Fr)", "data": "synthetic",
+            "mode": "single process, kzg_gpu_group C ABI (one host worker thread per device)",
+            "config": {"workload": "ONE BLS12-381 G1 MSM over 2^%d points from pinned host memory, split by point range over "
+                                   "%d devices; partials folded on device 0" % (args.log2n, G), "curve": CURVE},
+            "e2e": {"value": n / (msG * 1e-3), "unit": "points/s", "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": 96 + 4 + 192 * G,
+                    "ms_per_step": msG},
+            "one_device": {"ms_per_step": ms1, "speedup": ms1 / msG},
+            "commit": {"blobs": nb, "coeffs_per_blob": nc, "e2e": nb / (cG * 1e-3), "unit": "commits/s", "ms_e2e": cG,
+                       "one_device_ms": c1, "speedup": c1 / cG, "proofs_per_s_e2e": nb / (pG * 1e-3), "ms_prove_e2e": pG,
+                       "prove_speedup": p1 / pG},
+            "bytes_identical_to_one_device": True}
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -639,11 +697,15 @@ def main():
     ap.add_argument("--no-strong", action="store_true")
     ap.add_argument("--strong-log2n", default="20,22", help="sizes of the single MSMs split N ways (strong scaling)")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--single-process", action="store_true",
+                    help="drive --gpus N devices from ONE process through the kzg_gpu_group C ABI (no torchrun, no NCCL)")
     args = ap.parse_args()
     if args.impl == "reference":
         if args.ref_sample == 16384:
             args.ref_sample = 4096
         return run_reference(args)
+    if args.single_process:
+        return run_single_process(args)
     return run_b200(args)
 
 

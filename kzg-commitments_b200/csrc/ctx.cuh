@@ -256,8 +256,12 @@ struct Ctx final : kzg_gpu_ctx {
     // "table_pad" experiment: one 128-byte line per 96-byte point (BLS12-381), so a gathered point never straddles two lines
     g1_point_stride = opt_table_pad && sizeof(Affine<Fp>) <= 128 ? 128 : sizeof(Affine<Fp>);
     CK(g1_table.ensure((size_t)W * srs_n * g1_point_stride));
-    msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
-        srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>(), g1_point_stride);
+    if (srs_n <= TABLE_TEAM_MAX_POINTS)  // latency-bound build: four lanes per point (setup.cuh)
+      msm_precompute_table_team<Fp, MAXW><<<(unsigned)((4 * srs_n + 127) / 128), 128, 0, stream>>>(
+          srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>(), g1_point_stride);
+    else
+      msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
+          srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>(), g1_point_stride);
     LAUNCHED();
     CK(cudaStreamSynchronize(stream));
     table_c = c;
@@ -270,6 +274,7 @@ struct Ctx final : kzg_gpu_ctx {
   // drop-in in round 1: 36 ms on BLS12-381), and it is not built at all for SRS sizes where it would take gigabytes.
   // For the SRS sizes the reference's callers use (<= 65536 points) the build starts when the SRS becomes resident, on a
   // SIDE stream, so that neither the constructor nor the commitments that follow wait for it; the first G2 MSM does.
+  static constexpr uint64_t TABLE_TEAM_MAX_POINTS = 16384;  // up to ~one team per warp slot of the machine
   static constexpr uint64_t G2_TABLE_MIN_TERMS = 256;
   static constexpr uint64_t G2_TABLE_EAGER_MAX_SRS = 65536;
   cudaStream_t aux_stream = nullptr;
@@ -285,8 +290,12 @@ struct Ctx final : kzg_gpu_ctx {
     if (!g2_table_ev) CK(cudaEventCreateWithFlags(&g2_table_ev, cudaEventDisableTiming));
     CK(cudaEventRecord(g2_table_ev, stream));          // the SRS itself was written on the main stream
     CK(cudaStreamWaitEvent(aux_stream, g2_table_ev, 0));
-    msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, aux_stream>>>(
-        srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>(), sizeof(Affine<Fp2>));
+    if (srs_n <= TABLE_TEAM_MAX_POINTS)
+      msm_precompute_table_team<Fp2, MAXW><<<(unsigned)((4 * srs_n + 127) / 128), 128, 0, aux_stream>>>(
+          srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>(), sizeof(Affine<Fp2>));
+    else
+      msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, aux_stream>>>(
+          srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>(), sizeof(Affine<Fp2>));
     LAUNCHED();
     CK(cudaEventRecord(g2_table_ev, aux_stream));
     g2_table_pending = true;
@@ -328,7 +337,7 @@ struct Ctx final : kzg_gpu_ctx {
     last_batch = 0;
     if (inv_fact_n < 4096 && srs_n <= G2_TABLE_EAGER_MAX_SRS) {
       CK(inv_fact.ensure(4096 * sizeof(Fr)));
-      fr_inv_factorials<C><<<1, 32, 0, stream>>>(4096u, inv_fact.as<Fr>());
+      fr_inv_factorials<C><<<1, INV_FACT_THREADS, 0, stream>>>(4096u, inv_fact.as<Fr>());
       LAUNCHED();
       inv_fact_n = 4096;
     }
@@ -1128,7 +1137,7 @@ struct Ctx final : kzg_gpu_ctx {
     if (with_p && inv_fact_n < k) {  // 1/t! table (only the interpolant needs it), cached
       const uint64_t want = std::max<uint64_t>(kp, 4096);
       CK(inv_fact.ensure(want * sizeof(Fr)));
-      fr_inv_factorials<C><<<1, 32, 0, stream>>>((uint32_t)want, inv_fact.as<Fr>());
+      fr_inv_factorials<C><<<1, INV_FACT_THREADS, 0, stream>>>((uint32_t)want, inv_fact.as<Fr>());
       LAUNCHED();
       inv_fact_n = want;
     }

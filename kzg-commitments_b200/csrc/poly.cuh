@@ -303,22 +303,46 @@ poly_eval_range_kernel(uint64_t n, long long first_root, uint64_t k, const Field
 //      one launch per tree level.  The root holds I (first k coefficients) and Z (k + 1 coefficients).
 // k is padded to a power of two with c_j = 0, Z_j = 1 leaves, which changes neither I nor Z.
 
-// inv_fact[t] = 1 / t!  for t < n  (Montgomery).  One thread; cached by the context (a few ms once for n = 4096).
+// inv_fact[t] = 1 / t!  for t < n  (Montgomery), cached by the context.  One CTA: thread u owns a contiguous range of
+// integers, a suffix scan of the range products gives (n-1)! and every prod_{j >= hi_u} j, ONE inversion, then each
+// thread walks its range downwards: 1/(i-1)! = (1/i!) * i.  (Round 1 ran the 2n products on a single thread: 3 ms for
+// n = 4096, the first-call cliff of the multi-proof rows.)
+constexpr int INV_FACT_THREADS = 1024;
 template <class C>
-__global__ void fr_inv_factorials(uint32_t n, Field<typename C::FrP>* __restrict__ inv_fact) {
+__global__ void __launch_bounds__(INV_FACT_THREADS)
+fr_inv_factorials(uint32_t n, Field<typename C::FrP>* __restrict__ inv_fact) {
   using Fr = Field<typename C::FrP>;
-  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  __shared__ Fr s_prod[INV_FACT_THREADS];
+  __shared__ Fr s_inv;
+  const int tid = threadIdx.x, T = blockDim.x;
+  const uint32_t per = (n + T - 1) / T;
+  const uint32_t lo = min(per * (uint32_t)tid, n), hi = min(lo + per, n);
   const Fr one = Fr::one();
-  Fr f = one, t = one;  // f = i!, t = i (Montgomery)
-  for (uint32_t i = 1; i < n; i++) {
-    if (i > 1) t = Fr::add(t, one);
-    f = Fr::mul(f, t);
+  // product of the integers of [lo, hi) (0 counts as 1: 0! = 1)
+  Fr p = one, x = fr_from_i64<C>((long long)lo);
+  for (uint32_t i = lo; i < hi; i++) {
+    if (i > 0) p = Fr::mul(p, x);
+    x = Fr::add(x, one);
   }
-  Fr inv = Fr::inv(f);  // 1 / (n-1)!
-  for (uint32_t i = n; i-- > 0;) {
-    inv_fact[i] = inv;
-    inv = Fr::mul(inv, t);  // 1/(i-1)! = (1/i!) * i
-    t = Fr::sub(t, one);
+  s_prod[tid] = p;
+  __syncthreads();
+  for (int d = 1; d < T; d <<= 1) {  // inclusive suffix scan: s_prod[t] = prod of the ranges t, t+1, ...
+    Fr v = s_prod[tid];
+    const bool has = tid + d < T;
+    Fr v2 = has ? s_prod[tid + d] : one;
+    __syncthreads();
+    if (has) s_prod[tid] = Fr::mul(v, v2);
+    __syncthreads();
+  }
+  if (tid == 0) s_inv = Fr::inv(s_prod[0]);  // 1 / (n-1)!
+  __syncthreads();
+  // 1 / (hi-1)! = (1 / (n-1)!) * prod_{j >= hi} j
+  Fr inv = Fr::mul(s_inv, tid + 1 < T ? s_prod[tid + 1] : one);
+  x = fr_from_i64<C>((long long)hi - 1);
+  for (uint32_t i = hi; i-- > lo;) {
+    inv_fact[i] = inv;              // 1 / i!
+    if (i > 0) inv = Fr::mul(inv, x);  // 1/(i-1)! = (1/i!) * i
+    x = Fr::sub(x, one);
   }
 }
 

@@ -151,6 +151,53 @@ fixed_base_to_affine(uint64_t n, const XYZZ<F>* __restrict__ sums, Affine<F>* __
   }
 }
 
+// The same table with FOUR lanes per point (msm_team.cuh): the W * c doublings of a point are one dependent chain, and
+// for the SRS sizes the reference's callers use (a few thousand points) that chain, not the multiplier pipe, is the
+// build time — 256 doublings of 9 dependent products each on one thread (12 ms for the G2 table of a 5000-point
+// BLS12-381 SRS in round 1).  A team runs a doubling in 3 product rounds.  The normalisation is executed by all four
+// lanes on replicated values (same instructions, same warp: no extra issue slots) and written by the first.
+#if defined(__CUDACC__)
+template <class F, int MAXW>
+__global__ void __launch_bounds__(128)
+msm_precompute_table_team(uint64_t n, uint64_t stride, int c, int W, const Affine<F>* __restrict__ base,
+                          Affine<F>* __restrict__ table_ptr, size_t point_stride) {
+  const uint64_t i = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 2;
+  if (i >= n) return;  // whole teams leave together
+  const bool lead = (threadIdx.x & 3) == 0;
+  struct Strided {
+    char* p; size_t st;
+    __device__ Affine<F>& operator[](uint64_t k) const { return *reinterpret_cast<Affine<F>*>(p + k * st); }
+  } table{reinterpret_cast<char*>(table_ptr), point_stride};
+  const Affine<F> p0 = base[i];
+  if (lead) table[i] = p0;
+  if (p0.is_inf()) {
+    if (lead) for (int w = 1; w < W; w++) table[(uint64_t)w * stride + i] = p0;
+    return;
+  }
+  XYZZ<F> cur = XYZZ<F>::from_affine(p0);
+  XYZZ<F> pts[MAXW];
+  F pref[MAXW];
+  F run = F::one();
+  for (int w = 1; w < W; w++) {
+    for (int k = 0; k < c; k++) cur = team_dbl<F>(cur);
+    pts[w] = cur;
+    run = F::mul(run, cur.is_inf() ? F::one() : cur.ZZZ);
+    pref[w] = run;
+  }
+  F inv = F::inv(run);
+  for (int w = W - 1; w >= 1; w--) {
+    const F before = (w > 1) ? pref[w - 1] : F::one();
+    if (pts[w].is_inf()) { if (lead) table[(uint64_t)w * stride + i] = Affine<F>::inf(); continue; }
+    const F i3 = F::mul(inv, before);
+    inv = F::mul(inv, pts[w].ZZZ);
+    const F i1 = F::mul(pts[w].ZZ, i3);
+    const F i2 = F::sqr(i1);
+    const Affine<F> out{F::mul(pts[w].X, i2), F::mul(pts[w].Y, i3)};
+    if (lead) table[(uint64_t)w * stride + i] = out;
+  }
+}
+#endif
+
 // MSM window table:  table[w * stride + i] = 2^(c*w) * base[i],  w < W  (row 0 = the SRS itself).
 // One thread per point; the W projective values are normalised with ONE inversion (Montgomery's
 // trick over the thread's own W values), which is why the scratch lives in local memory.
