@@ -73,6 +73,9 @@ void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
  * 3 = default: power-series inversion with truncated products over the whole GPU), "affine_levels" (batched-affine
  * pre-reduction levels, -1 = auto = off), "finish_affine" (0: an MSM leaves only its projective result for
  * kzg_gpu_msm_partial_device — the point-range split folds and normalises once, after the exchange).
+ * "tail" (1: the sort and the narrow end of the reduction run in two persistent cooperative kernels), "tail_proj" (1: that
+ * end uses complete projective formulas on 8-lane teams for G1), "table_pad" (experiment: 128-byte window-table entries),
+ * "barrier_sleep" (ns between polls of the grid barrier).
  * Takes effect at the next srs_load / setup_powers / MSM. */
 int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value);
 
@@ -169,7 +172,10 @@ int kzg_gpu_msm_stats(kzg_gpu_ctx* ctx, uint64_t* out, int n);
  * kind 0: independent mad.lo.cc/madc.hi.cc chains (-> IMAD.WIDE.U32.X), returns 32x32 products/s
  * kind 1: independent plain 32-bit IMAD (mad.lo.u32), returns instructions/s
  * kind 2: Fp Montgomery products/s of the context's curve (register-resident operands)
- * kind 3: Fr Montgomery products/s */
+ * kind 3: Fr Montgomery products/s
+ * kinds 4..7: LATENCY probes in the configuration of the reduction tail (one CTA of 128 threads per SM), returned as
+ * steps per second of ONE dependent chain: 4 = grid barriers, 5 = 4-lane team additions (XYZZ, G1 field),
+ * 6 = single-thread additions, 7 = dependent Fp Montgomery products */
 int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops_per_second);
 
 /* Device self-test: field, Fp2 and group-law identities on random inputs, compared on device against

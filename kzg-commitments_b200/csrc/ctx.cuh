@@ -23,6 +23,7 @@
 #include "msm_affine.cuh"
 #include "msm_team.cuh"
 #include "msm_tail.cuh"
+#include "msm_tail_proj.cuh"
 #include "poly.cuh"
 #include "setup.cuh"
 
@@ -72,7 +73,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1, opt_table_pad = 0;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1, opt_table_pad = 0, opt_barrier_sleep = 64, opt_tail_proj = 1;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -112,12 +113,13 @@ struct kzg_gpu_ctx {
     coop_blocks[kernel] = v;
     return v;
   }
-  int launch_cooperative(const void* kernel, uint64_t blocks_wanted, int threads, void* args_struct, size_t smem = 0) {
+  int launch_cooperative(const void* kernel, uint64_t blocks_wanted, int threads, void* args_struct, size_t smem = 0,
+                         void* second_arg = nullptr) {
     int cap = max_cooperative_blocks(kernel, threads);
     if (cap <= 0) { last_error = "cooperative launch: kernel does not fit the device"; return KZG_GPU_ERR_CUDA; }
     if (num_sms > 0) cap = std::min(cap, num_sms);  // one CTA per SM: cheap grid barriers, one warp per sub-partition
     const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(blocks_wanted, (uint64_t)cap));
-    void* params[1] = {args_struct};
+    void* params[2] = {args_struct, second_arg};
     cudaError_t e = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3((unsigned)threads), params, smem, stream);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchCooperativeKernel");
     launches++;
@@ -406,15 +408,31 @@ struct Ctx final : kzg_gpu_ctx {
   // msm_tail<F>: one CTA of TAIL_THREADS per SM; the dynamic shared-memory request only keeps a second CTA off the SM
   template <class F>
   int prepare_tail() {
-    if (tail_ready[std::is_same<F, Fp2>::value ? 1 : 0]) return KZG_GPU_OK;
+    if (tail_ready[std::is_same<F, Fp2>::value ? 1 : 0]) return ensure_barrier();
     CK(cudaFuncSetAttribute(msm_tail<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
-    if (!barrier_buf.p) {
-      CK(barrier_buf.ensure(sizeof(GridBarrier)));
-      CK(cudaMemsetAsync(barrier_buf.p, 0, sizeof(GridBarrier), stream));
-    }
+    if constexpr (std::is_same<F, Fp>::value)
+      CK(cudaFuncSetAttribute(msm_tail_proj<Fp>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
+    int rcb = ensure_barrier();
+    if (rcb) return rcb;
     tail_ready[std::is_same<F, Fp2>::value ? 1 : 0] = true;
     return KZG_GPU_OK;
   }
+  int ensure_barrier() {
+    if (!barrier_buf.p) {
+      CK(barrier_buf.ensure(sizeof(GridBarrier)));
+      CK(cudaMemsetAsync(barrier_buf.p, 0, sizeof(GridBarrier), stream));
+      barrier_sleep_set = -1;
+    }
+    if (barrier_sleep_set != opt_barrier_sleep) {
+      const unsigned v = (unsigned)opt_barrier_sleep;
+      CK(cudaMemcpyAsync(reinterpret_cast<char*>(barrier_buf.p) + offsetof(GridBarrier, sleep_ns), &v, sizeof v,
+                         cudaMemcpyHostToDevice, stream));
+      CK(cudaStreamSynchronize(stream));  // `v` is a stack variable
+      barrier_sleep_set = opt_barrier_sleep;
+    }
+    return KZG_GPU_OK;
+  }
+  int barrier_sleep_set = -1;
   bool tail_ready[2] = {false, false};
   DevBuf barrier_buf;
   uint64_t tail_threads_total() {
@@ -608,6 +626,12 @@ struct Ctx final : kzg_gpu_ctx {
       ta.rin = rin; ta.rout = rout; ta.cin = cin; ta.cout = cout;
       ta.r_len = r_len; ta.c_len = c_len;
       (void)items;  // always one CTA per SM: narrow levels are dealt out one warp per SM first (msm_tail.cuh)
+      if constexpr (std::is_same<F, Fp>::value) {
+        if (opt_tail_proj) {  // G1: complete projective formulas on 8-lane teams, two product rounds per addition
+          int b3 = 3 * C::G1_B;
+          return launch_cooperative((const void*)msm_tail_proj<Fp>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES, &b3);
+        }
+      }
       return launch_cooperative((const void*)msm_tail<F>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES);
     };
     const int tail_last = finish_in_tail ? TAIL_FINISH : TAIL_COMBINE;
@@ -950,10 +974,8 @@ struct Ctx final : kzg_gpu_ctx {
     const bool series = cost_series < cost_cta && cost_series < cost_grid;
     const bool rounds_grid = !series && cost_grid < cost_cta && opt_long_division >= 3;
     if (rounds_grid) {
-      if (!barrier_buf.p) {
-        CK(barrier_buf.ensure(sizeof(GridBarrier)));
-        CK(cudaMemsetAsync(barrier_buf.p, 0, sizeof(GridBarrier), stream));
-      }
+      int rcb = ensure_barrier();
+      if (rcb) return rcb;
       constexpr int QG = 256;
       CK(tile_sums.ensure(2 * 1024 * sizeof(Fr)));
       struct { uint64_t n; long long first_root; uint64_t k; Fr* b0; Fr* b1; Fr* agg; GridBarrier* bar; } qa{
@@ -1354,8 +1376,9 @@ struct Ctx final : kzg_gpu_ctx {
   int microbench(int kind, double* ops) override {
     std::lock_guard<std::recursive_mutex> lock(mu);
     CK(cudaSetDevice(device));
-    if (!ops || kind < 0 || kind > 3) return KZG_GPU_ERR_ARG;
+    if (!ops || kind < 0 || kind > 7) return KZG_GPU_ERR_ARG;
     CK(scal.ensure(64));
+    if (kind >= 4) return microbench_latency(kind, ops);
     const int blocks = 148 * 8, threads = 256;
     int iters = kind <= 1 ? 4096 : 256;
     double per_thread_iter = kind == 0 ? 32.0 : kind == 1 ? 16.0 : 2.0;
@@ -1381,6 +1404,44 @@ struct Ctx final : kzg_gpu_ctx {
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     *ops = (double)blocks * threads * iters * per_thread_iter / (best * 1e-3);
+    return KZG_GPU_OK;
+  }
+
+  // kinds 4..7: latency of one grid barrier / team addition / single-thread addition / Montgomery product (G1 field), in
+  // the msm_tail configuration (one CTA of 128 threads per SM).  *ops = steps per second of ONE dependent chain.
+  int microbench_latency(int kind, double* ops) {
+    int rc = prepare_tail<Fp>();
+    if (rc) return rc;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int iters = kind == 4 ? 2000 : kind == 7 ? 4000 : 400;
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; rep++) {
+      CK(cudaEventRecord(e0, stream));
+      if (kind == 4) {
+        int it = iters;
+        GridBarrier* bar = barrier_buf.as<GridBarrier>();
+        void* params[2] = {&it, &bar};
+        const void* kern = (const void*)bench_grid_barrier;
+        int cap = max_cooperative_blocks(kern, TAIL_THREADS);
+        if (cap <= 0) return KZG_GPU_ERR_CUDA;
+        cap = std::min(cap, num_sms > 0 ? num_sms : cap);
+        CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)cap), dim3(TAIL_THREADS), params, 0, stream));
+        launches++;
+      } else {
+        bench_latency_chain<Fp><<<num_sms > 0 ? num_sms : 148, TAIL_THREADS, 0, stream>>>(kind, iters, 777u + rep, scal.as<uint32_t>());
+        LAUNCHED();
+      }
+      CK(cudaEventRecord(e1, stream));
+      CK(cudaEventSynchronize(e1));
+      float ms = 0;
+      CK(cudaEventElapsedTime(&ms, e0, e1));
+      if (rep > 0) best = std::min(best, ms);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ops = (double)iters / (best * 1e-3);
     return KZG_GPU_OK;
   }
 

@@ -13,6 +13,8 @@ struct GridBarrier {        // lives in device memory, zero-initialised once; re
   unsigned pad0[31];
   unsigned gen;
   unsigned pad1[31];
+  unsigned sleep_ns;      // pause between two polls of `gen` (0 = poll back to back); "barrier_sleep" option
+  unsigned pad2[31];
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
@@ -32,7 +34,9 @@ __device__ __forceinline__ void grid_sync(GridBarrier* b) {
       __threadfence();
       atomicAdd(&b->gen, 1u);
     } else {
-      while (ld_acquire_u32(&b->gen) == g) __nanosleep(64);
+      const unsigned pause = b->sleep_ns;
+      while (ld_acquire_u32(&b->gen) == g)
+        if (pause) __nanosleep(pause);
     }
     __threadfence();
   }

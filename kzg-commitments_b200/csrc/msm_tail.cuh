@@ -339,5 +339,32 @@ __global__ void __launch_bounds__(SCAN_THREADS) msm_sort_small(SortArgs a) {
   msm_task_place_body(a.nbuckets, a.task_chunk, a.starts, a.task_first, a.hist_start, a.hist_cursor, a.tasks, a.slot_seg);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Latency microbenchmarks behind kzg_gpu_microbench kinds 4..7 ("what bounds the tail"): the cost
+// of one grid barrier, and of ONE dependent step of each kind with operands in registers and one warp per SM
+// sub-partition — the numbers the step count of msm_tail has to be multiplied with.
+static __global__ void __launch_bounds__(TAIL_THREADS, 1) bench_grid_barrier(int iters, GridBarrier* bar) {
+  for (int i = 0; i < iters; i++) grid_sync(bar);
+}
+template <class F>
+__global__ void __launch_bounds__(TAIL_THREADS, 1) bench_latency_chain(int kind, int iters, uint32_t seed, uint32_t* sink) {
+  // a valid-looking (not necessarily on-curve) pair of projective points: the formulas do not care
+  XYZZ<F> acc, p;
+  F t = F::one();
+  t.v[0] ^= (seed & 0xffu) + 3u;
+  acc.X = F::mul(t, F::r2()); acc.Y = F::sqr(acc.X); acc.ZZ = F::mul(acc.Y, t); acc.ZZZ = F::sqr(acc.ZZ);
+  p.X = F::sqr(acc.ZZZ); p.Y = F::mul(p.X, t); p.ZZ = F::sqr(p.Y); p.ZZZ = F::mul(p.ZZ, acc.X);
+  F m = acc.X;
+  for (int it = 0; it < iters; it++) {
+    if (kind == 5) acc = team_add<F>(acc, p);   // 4 lanes per addition: 5 product rounds
+    else if (kind == 6) acc.add(p);             // one thread per addition: 14 dependent products
+    else m = F::mul(m, p.X);                    // kind 7: one dependent Montgomery product
+  }
+  uint32_t o = 0;
+#pragma unroll
+  for (int i = 0; i < Field<typename F::Params>::L; i++) o ^= acc.X.v[i] ^ acc.ZZZ.v[i] ^ m.v[i];
+  if (o == 0x12345678u) sink[0] = o;
+}
+
 }  // namespace kzgb200
 #endif

@@ -1,0 +1,419 @@
+// The reduction tail of a G1 MSM in HOMOGENEOUS PROJECTIVE coordinates on 8-lane teams.
+//
+// Measured (kzg_gpu_microbench kinds 4..7, profiles/r2g_latency.json): one dependent Fp Montgomery product on a warp
+// that has its SM sub-partition to itself takes 1.05 us, a 4-lane XYZZ addition (msm_team.cuh: 14 products, FIVE
+// dependent rounds) 6.7 us, a grid barrier 2.3 us — a step of msm_tail costs ~10.5 us and a 2^12-point MSM is ~40
+// such steps deep.  The depth in product ROUNDS is what can still be cut: the complete addition formulas of Renes,
+// Costello and Batina for y^2 = x^3 + b (a = 0; "Complete addition formulas for prime order elliptic curves",
+// Algorithms 7 and 9) need 12 products in only TWO rounds of six independent ones, and a doubling 8 products in two
+// rounds of four, because the multiplications by 3b are a few additions when b is small (b = 5, 2, 4 on the three
+// curves of this library).  One operation per 8 adjacent lanes: lanes 0-5 take the six products of a round, the
+// linear steps run replicated.  The formulas are complete for curves of odd order (all three), so infinity (0 : 1 : 0),
+// P + P and P + (-P) need no branches.
+//
+// msm_tail_proj is msm_tail (msm_tail.cuh) with these operations for every step that is narrow enough for the
+// 8-lane teams; the fold of the task partials (in place on the XYZZ partials that the wide kernels also read) and
+// levels of more than 4 rounds of teams keep XYZZ, converted on first use (X ZZZ : Y ZZ : ZZ ZZZ, one round).
+// G2 keeps msm_tail: its 3b' is a general Fp2 element on the D-type twists.
+#pragma once
+#include "msm_tail.cuh"
+
+#if defined(__CUDACC__)
+namespace kzgb200 {
+
+template <class F>
+struct Proj {
+  F X, Y, Z;
+  __device__ __forceinline__ bool is_inf() const { return Z.is_zero(); }
+};
+
+struct Octet {
+  int role, base;
+  unsigned mask;
+  __device__ __forceinline__ Octet() {
+    const int lane = threadIdx.x & 31;
+    role = lane & 7;
+    base = lane & ~7;
+    mask = 0xFFu << base;
+  }
+};
+
+// k * x for a small positive k (3b <= 15) by doubling and adding
+template <class F>
+__device__ __forceinline__ F mul_small(const F& x, int k) {
+  F r = x;
+  int bit = 31 - __clz(k);
+  for (bit--; bit >= 0; bit--) {
+    r = F::dbl(r);
+    if ((k >> bit) & 1) r = F::add(r, x);
+  }
+  return r;
+}
+
+// a + b, complete (RCB Algorithm 7 with a = 0, b3 = 3b).  a, b and the result are replicated on the 8 lanes.
+template <class F>
+__device__ __noinline__ Proj<F> oct_add(const Proj<F>& a, const Proj<F>& b, int b3) {
+  const Octet tm;
+  const int r = tm.role, base = tm.base;
+  const unsigned mask = tm.mask;
+  // round 1:  X1X2 | Y1Y2 | Z1Z2 | (X1+Y1)(X2+Y2) | (Y1+Z1)(Y2+Z2) | (X1+Z1)(X2+Z2)
+  F u = r == 0 ? a.X : r == 1 ? a.Y : a.Z, v = r == 0 ? b.X : r == 1 ? b.Y : b.Z;
+  if (r >= 3) {  // (uniform inside a team only per lane: both sides are cheap, the compiler predicates them)
+    u = F::add(r == 4 ? a.Y : a.X, r == 3 ? a.Y : a.Z);
+    v = F::add(r == 4 ? b.Y : b.X, r == 3 ? b.Y : b.Z);
+  }
+  const F m1 = F::mul(u, v);
+  const F t0 = team_shfl(mask, m1, base), t1o = team_shfl(mask, m1, base + 1), t2o = team_shfl(mask, m1, base + 2);
+  F t3 = team_shfl(mask, m1, base + 3), t4 = team_shfl(mask, m1, base + 4), y3 = team_shfl(mask, m1, base + 5);
+  t3 = F::sub(F::sub(t3, t0), t1o);                // X1Y2 + X2Y1
+  t4 = F::sub(F::sub(t4, t1o), t2o);               // Y1Z2 + Y2Z1
+  y3 = mul_small(F::sub(F::sub(y3, t0), t2o), b3); // b3 (X1Z2 + X2Z1)
+  const F x3 = F::add(F::dbl(t0), t0);             // 3 X1X2
+  const F t2 = mul_small(t2o, b3);                 // b3 Z1Z2
+  const F z3 = F::add(t1o, t2), t1 = F::sub(t1o, t2);
+  // round 2:  t4 y3 | t3 t1 | y3 x3 | t1 z3 | x3 t3 | z3 t4
+  const F p = r == 0 ? t4 : r == 1 ? t3 : r == 2 ? y3 : r == 3 ? t1 : r == 4 ? x3 : z3;
+  const F q = r == 0 ? y3 : r == 1 ? t1 : r == 2 ? x3 : r == 3 ? z3 : r == 4 ? t3 : t4;
+  const F m2 = F::mul(p, q);
+  Proj<F> o;
+  o.X = F::sub(team_shfl(mask, m2, base + 1), team_shfl(mask, m2, base));
+  o.Y = F::add(team_shfl(mask, m2, base + 3), team_shfl(mask, m2, base + 2));
+  o.Z = F::add(team_shfl(mask, m2, base + 5), team_shfl(mask, m2, base + 4));
+  return o;
+}
+
+// 2 a, complete (RCB Algorithm 9 with a = 0)
+template <class F>
+__device__ __noinline__ Proj<F> oct_dbl(const Proj<F>& a, int b3) {
+  const Octet tm;
+  const int r = tm.role, base = tm.base;
+  const unsigned mask = tm.mask;
+  // round 1:  Y Y | Y Z | Z Z | X Y
+  const F m1 = F::mul(r == 2 ? a.Z : r >= 3 ? a.X : a.Y, r == 0 || r >= 3 ? a.Y : a.Z);
+  const F t0 = team_shfl(mask, m1, base), t1 = team_shfl(mask, m1, base + 1), xy = team_shfl(mask, m1, base + 3);
+  const F t2 = mul_small(team_shfl(mask, m1, base + 2), b3);  // b3 Z^2
+  const F z8 = F::dbl(F::dbl(F::dbl(t0)));                    // 8 Y^2
+  const F y3 = F::add(t0, t2);
+  const F t0m = F::sub(t0, F::add(F::dbl(t2), t2));           // Y^2 - 3 b3 Z^2
+  // round 2:  t2 z8 | t1 z8 | t0m y3 | t0m xy
+  const F m2 = F::mul(r == 0 ? t2 : r == 1 ? t1 : t0m, r <= 1 ? z8 : r == 2 ? y3 : xy);
+  Proj<F> o;
+  o.Y = F::add(team_shfl(mask, m2, base), team_shfl(mask, m2, base + 2));
+  o.Z = team_shfl(mask, m2, base + 1);
+  o.X = F::dbl(team_shfl(mask, m2, base + 3));
+  return o;
+}
+
+// two XYZZ values -> projective in ONE round: (X ZZZ : Y ZZ : ZZ ZZZ); XYZZ infinity (ZZ = 0) -> (0 : 1 : 0)
+template <class F>
+__device__ __noinline__ void oct_from_xyzz2(const XYZZ<F>& a, const XYZZ<F>& b, Proj<F>& pa, Proj<F>& pb) {
+  const Octet tm;
+  const int r = tm.role, base = tm.base;
+  const unsigned mask = tm.mask;
+  const bool second = r >= 3 && r < 6;
+  const XYZZ<F>& s = second ? b : a;
+  const int k = second ? r - 3 : (r < 3 ? r : 0);
+  const F m = F::mul(k == 0 ? s.X : k == 1 ? s.Y : s.ZZ, k == 1 ? s.ZZ : s.ZZZ);
+  pa.X = team_shfl(mask, m, base); pa.Y = team_shfl(mask, m, base + 1); pa.Z = team_shfl(mask, m, base + 2);
+  pb.X = team_shfl(mask, m, base + 3); pb.Y = team_shfl(mask, m, base + 4); pb.Z = team_shfl(mask, m, base + 5);
+  if (a.is_inf()) { pa.X = F::zero(); pa.Y = F::one(); pa.Z = F::zero(); }
+  if (b.is_inf()) { pb.X = F::zero(); pb.Y = F::one(); pb.Z = F::zero(); }
+}
+
+// projective -> XYZZ (X Z : Y Z^2 : Z^2 : Z^3) for the callers that exchange projective partial sums as XYZZ
+template <class F>
+__device__ __noinline__ XYZZ<F> oct_to_xyzz(const Proj<F>& a) {
+  const Octet tm;
+  const int r = tm.role, base = tm.base;
+  const unsigned mask = tm.mask;
+  const F m1 = F::mul(r == 0 ? a.X : a.Z, a.Z);  // X Z | Z^2
+  const F xz = team_shfl(mask, m1, base), zz = team_shfl(mask, m1, base + 1);
+  const F m2 = F::mul(r == 0 ? a.Y : a.Z, zz);   // Y Z^2 | Z^3
+  XYZZ<F> o;
+  o.X = xz;
+  o.Y = team_shfl(mask, m2, base);
+  o.ZZ = zz;
+  o.ZZZ = team_shfl(mask, m2, base + 1);
+  if (a.is_inf()) o = XYZZ<F>::inf();
+  return o;
+}
+
+template <class F>
+__device__ Proj<F> oct_small_mul(const Proj<F>& p, uint32_t k, int b3) {
+  Proj<F> m{F::zero(), F::one(), F::zero()};
+  if (k == 0) return m;
+  for (int bit = top_bit_u32(k); bit >= 0; bit--) {
+    m = oct_dbl<F>(m, b3);
+    if ((k >> bit) & 1) m = oct_add<F>(m, p, b3);
+  }
+  return m;
+}
+
+// an array that holds either XYZZ values (written by the wide kernels / thread-mode levels) or projective ones
+template <class F>
+struct MixedArray {
+  XYZZ<F>* p;
+  bool xyzz;
+  __device__ __forceinline__ Proj<F>* proj() const { return reinterpret_cast<Proj<F>*>(p); }
+};
+
+// elements i and j of `in` as projective values (one conversion round when the array still holds XYZZ)
+template <class F>
+__device__ __forceinline__ void oct_load2(const MixedArray<F>& in, uint64_t i, uint64_t j, Proj<F>& a, Proj<F>& b) {
+  if (in.xyzz) {
+    const XYZZ<F> x = in.p[i], y = in.p[j];
+    oct_from_xyzz2<F>(x, y, a, b);
+  } else {
+    a = in.proj()[i];
+    b = in.proj()[j];
+  }
+}
+
+struct OctLane {
+  uint64_t oct, nocts;
+  bool lead;
+  __device__ __forceinline__ OctLane(const TailLane& tl) {
+    oct = tl.vwarp * 4 + (tl.lane >> 3);
+    nocts = tl.nvwarps * 4;
+    lead = (tl.lane & 7) == 0;
+  }
+  // a level runs on 8-lane teams while that takes at most four rounds
+  __device__ __forceinline__ bool fits(uint64_t items) const { return items <= 4 * nocts; }
+};
+
+// one level of the two pairwise trees; switches an array to projective the first time its level fits the teams
+template <class F>
+__device__ __forceinline__ void tailp_pair_level(const TailLane& tl, const OctLane& ol, MixedArray<F>& in0, MixedArray<F>& out0,
+                                                 uint64_t n0, MixedArray<F>& in1, MixedArray<F>& out1, uint64_t n1, int b3) {
+  const bool octs = ol.fits(n0 + n1) || (n0 && !in0.xyzz) || (n1 && !in1.xyzz);
+  if (octs) {
+    for (uint64_t t = ol.oct; t < n0 + n1; t += ol.nocts) {
+      const bool second = t >= n0;
+      const uint64_t i = second ? t - n0 : t;
+      Proj<F> a, b;
+      oct_load2<F>(second ? in1 : in0, 2 * i, 2 * i + 1, a, b);
+      const Proj<F> s = oct_add<F>(a, b, b3);
+      if (ol.lead) (second ? out1 : out0).proj()[i] = s;
+    }
+    if (n0) out0.xyzz = false;
+    if (n1) out1.xyzz = false;
+  } else {
+    for (uint64_t t = tl.thread(); t < n0 + n1; t += tl.nthreads()) {
+      const bool second = t >= n0;
+      const uint64_t i = second ? t - n0 : t;
+      const XYZZ<F>* in = second ? in1.p : in0.p;
+      XYZZ<F> acc = in[2 * i];
+      acc.add(in[2 * i + 1]);
+      (second ? out1.p : out0.p)[i] = acc;
+    }
+    if (n0) out0.xyzz = true;
+    if (n1) out1.xyzz = true;
+  }
+}
+
+template <class F>
+__device__ __forceinline__ void tailp_trees(const TailLane& tl, const OctLane& ol, GridBarrier* bar, MixedArray<F>& in0,
+                                            MixedArray<F>& out0, uint64_t sums0, uint64_t& len0, MixedArray<F>& in1,
+                                            MixedArray<F>& out1, uint64_t sums1, uint64_t& len1, int b3) {
+  while (len0 > 1 || len1 > 1) {
+    tailp_pair_level<F>(tl, ol, in0, out0, len0 > 1 ? sums0 * (len0 / 2) : 0, in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0, b3);
+    if (len0 > 1) { MixedArray<F> t = in0; in0 = out0; out0 = t; len0 /= 2; }
+    if (len1 > 1) { MixedArray<F> t = in1; in1 = out1; out1 = t; len1 /= 2; }
+    grid_sync(bar);
+  }
+}
+
+template <class F>
+__global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, int b3) {
+  const TailLane tl;
+  const OctLane ol(tl);
+  const bool lead4 = (threadIdx.x & 3) == 0;
+  // arrays produced before this launch (wide kernels) hold XYZZ values
+  MixedArray<F> rin{a.rin, true}, rout{a.rout, true}, cin{a.cin, true}, cout{a.cout, true};
+  bool group_xyzz = true;
+  uint64_t r_len = a.r_len, c_len = a.c_len;
+
+  if (a.first_stage <= TAIL_FOLD && a.last_stage >= TAIL_FOLD) {
+    // in place on the XYZZ task partials (the wide kernels read them too): 4-lane XYZZ teams as in msm_tail
+    const uint32_t max_nt = *a.max_nt, ntasks = *a.ntasks_ptr;
+    for (uint32_t stride = 1; stride < max_nt; stride <<= 1) {
+      for (uint64_t q0 = tl.vwarp * 32; q0 < ntasks; q0 += tl.nvwarps * 32) {
+        const uint64_t q = q0 + tl.lane;
+        bool work = false;
+        if (q < ntasks) {
+          const MsmSlotSeg sg = a.slot_seg[q];
+          work = (sg.k & (2u * stride - 1u)) == 0u && sg.k + stride < sg.nt;
+        }
+        unsigned pending = __ballot_sync(0xffffffffu, work);
+        while (pending) {
+          const int my = tl.lane >> 2;
+          unsigned m = pending;
+          int pick = -1;
+          for (int k = 0; k <= my && m; k++) {
+            pick = __ffs(m) - 1;
+            m &= m - 1;
+            if (k < my) pick = -1;
+          }
+          if (pick >= 0) {
+            const uint64_t qq = q0 + pick;
+            const XYZZ<F> x = a.partial[qq], y = a.partial[qq + stride];
+            const XYZZ<F> s = team_add<F>(x, y);
+            __syncwarp(Team().mask);
+            if (lead4) a.partial[qq] = s;
+          }
+          for (int k = 0; k < 8 && pending; k++) pending &= pending - 1;
+        }
+      }
+      grid_sync(a.barrier);
+    }
+  }
+  if (a.first_stage <= TAIL_BUCKET_PAIRS && a.last_stage >= TAIL_BUCKET_PAIRS) {
+    const uint64_t Lr = a.Cn >= 2 ? a.Cn / 2 : 1, Lc = a.R >= 2 ? a.R / 2 : 1;
+    const BucketJob<F> jr{rin.p, a.R, a.Cn, a.Cn, 1, a.groups * a.R * Lr};
+    const BucketJob<F> jc{cin.p, a.Cn, a.R, 1, a.Cn, a.groups * a.Cn * Lc};
+    const uint64_t total = jr.total + jc.total;
+    if (ol.fits(total)) {
+      for (uint64_t t0 = ol.oct; t0 < total; t0 += ol.nocts) {
+        const bool second = t0 >= jr.total;
+        const BucketJob<F>& jb = second ? jc : jr;
+        const uint64_t t = second ? t0 - jr.total : t0;
+        const uint64_t P = jb.len >= 2 ? jb.len / 2 : 1;
+        const uint64_t p = t % P, gs = t / P;
+        const uint64_t s = gs % jb.nsums, g = gs / jb.nsums;
+        const uint64_t b0 = g * a.nb + s * jb.sstride + 2 * p * jb.jstride;
+        const XYZZ<F> x = bucket_value<F>(a.task_first, a.partial, b0);
+        const XYZZ<F> y = jb.len >= 2 ? bucket_value<F>(a.task_first, a.partial, b0 + jb.jstride) : XYZZ<F>::inf();
+        Proj<F> pa, pb;
+        oct_from_xyzz2<F>(x, y, pa, pb);
+        const Proj<F> acc = oct_add<F>(pa, pb, b3);
+        if (ol.lead) (second ? cin : rin).proj()[t] = acc;
+      }
+      rin.xyzz = cin.xyzz = false;
+    } else {
+      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+        const bool second = t0 >= jr.total;
+        msm_bucket_pair_thread<F>(second ? jc : jr, a.nb, a.task_first, a.partial, second ? t0 - jr.total : t0);
+      }
+    }
+    r_len = Lr;
+    c_len = Lc;
+    grid_sync(a.barrier);
+  }
+  if (a.first_stage <= TAIL_TREES1 && a.last_stage >= TAIL_TREES1)
+    tailp_trees<F>(tl, ol, a.barrier, rin, rout, a.groups * a.R, r_len, cin, cout, a.groups * a.Cn, c_len, b3);
+  if (a.first_stage <= TAIL_WEIGHTED && a.last_stage >= TAIL_WEIGHTED) {
+    const uint64_t Pr = a.R >= WCHUNK ? a.R / WCHUNK : 1, Pc = a.Cn >= WCHUNK ? a.Cn / WCHUNK : 1;
+    const uint64_t total_r = a.groups * Pr, total_c = a.groups * Pc, total = total_r + total_c;
+    if (ol.fits(total) || !rin.xyzz || !cin.xyzz) {
+      static_assert(WCHUNK == 2, "the projective weighted step is written for chunks of two");
+      for (uint64_t t0 = ol.oct; t0 < total; t0 += ol.nocts) {
+        const bool second = t0 >= total_r;
+        const uint64_t t = second ? t0 - total_r : t0;
+        const uint64_t m = second ? a.Cn : a.R;
+        const MixedArray<F>& in = second ? cin : rin;
+        const uint32_t woff = second ? 1u : 0u;
+        const uint64_t P = m >= WCHUNK ? m / WCHUNK : 1;
+        const uint64_t p = t % P, g = t / P;
+        const uint64_t j0i = p * WCHUNK;
+        // chunk {j0, j0 + 1} (or {j0} alone when m == 1): acc = v0 + 2 v1, run = v0 + v1 (msm_weighted_chunk_thread)
+        Proj<F> v0, v1;
+        oct_load2<F>(in, g * m + j0i, g * m + (m >= 2 ? j0i + 1 : j0i), v0, v1);
+        Proj<F> run = v0, acc = v0;
+        if (m >= 2) {
+          run = oct_add<F>(v1, v0, b3);
+          acc = oct_add<F>(v1, run, b3);
+        }
+        const uint32_t k = (uint32_t)j0i + woff;  // weights wanted: j + woff = (j - j0 + 1) + (k - 1)
+        if (k >= 1) acc = oct_add<F>(acc, oct_small_mul<F>(run, k - 1, b3), b3);
+        else {
+          run.Y = F::neg(run.Y);
+          acc = oct_add<F>(acc, run, b3);
+        }
+        if (ol.lead) (second ? cout : rout).proj()[t] = acc;
+      }
+      rout.xyzz = cout.xyzz = false;
+    } else {
+      const WeightedJob<F> wr{rin.p, rout.p, a.R, total_r, 0u};
+      const WeightedJob<F> wc{cin.p, cout.p, a.Cn, total_c, 1u};
+      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+        const bool second = t0 >= wr.total;
+        msm_weighted_chunk_thread<F>(second ? wc : wr, second ? t0 - wr.total : t0);
+      }
+      rout.xyzz = cout.xyzz = true;
+    }
+    { MixedArray<F> t = rin; rin = rout; rout = t; }
+    { MixedArray<F> t = cin; cin = cout; cout = t; }
+    r_len = Pr;
+    c_len = Pc;
+    grid_sync(a.barrier);
+  }
+  if (a.first_stage <= TAIL_TREES2 && a.last_stage >= TAIL_TREES2)
+    tailp_trees<F>(tl, ol, a.barrier, rin, rout, a.groups, r_len, cin, cout, a.groups, c_len, b3);
+  if (a.first_stage <= TAIL_COMBINE && a.last_stage >= TAIL_COMBINE) {
+    // group_out[g] = 2^h * T1[g] + T2[g]
+    if (ol.fits(a.groups) || !rin.xyzz || !cin.xyzz) {
+      Proj<F>* gout = reinterpret_cast<Proj<F>*>(a.group_out);
+      for (uint64_t g = ol.oct; g < a.groups; g += ol.nocts) {
+        Proj<F> acc, b;
+        if (rin.xyzz == cin.xyzz && rin.xyzz) {
+          const XYZZ<F> x = rin.p[g], y = cin.p[g];
+          oct_from_xyzz2<F>(x, y, acc, b);
+        } else {
+          Proj<F> dummy;
+          if (rin.xyzz) { const XYZZ<F> x = rin.p[g]; oct_from_xyzz2<F>(x, x, acc, dummy); } else acc = rin.proj()[g];
+          if (cin.xyzz) { const XYZZ<F> y = cin.p[g]; oct_from_xyzz2<F>(y, y, b, dummy); } else b = cin.proj()[g];
+        }
+        for (int k = 0; k < a.h; k++) acc = oct_dbl<F>(acc, b3);
+        acc = oct_add<F>(acc, b, b3);
+        if (ol.lead) gout[g] = acc;
+      }
+      group_xyzz = false;
+    } else {
+      for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads()) msm_group_combine_thread<F>(a.h, rin.p, cin.p, a.group_out, g);
+    }
+    if (a.last_stage >= TAIL_FINISH) grid_sync(a.barrier);
+  }
+  if (a.first_stage <= TAIL_FINISH && a.last_stage >= TAIL_FINISH) {
+    // one MSM per WARP (its first 8 lanes): the inversion is a data-dependent loop
+    if (tl.lane < 8) {
+      const Proj<F>* gp = reinterpret_cast<const Proj<F>*>(a.group_out);
+      for (uint64_t m = tl.vwarp; m < a.batch; m += tl.nvwarps) {
+        auto load = [&](uint64_t idx) -> Proj<F> {
+          if (!group_xyzz) return gp[idx];
+          Proj<F> v, dummy;
+          const XYZZ<F> x = a.group_out[idx];
+          oct_from_xyzz2<F>(x, x, v, dummy);
+          return v;
+        };
+        Proj<F> acc = load(m * a.groups_per_msm + (a.groups_per_msm - 1));
+        for (int g = a.groups_per_msm - 2; g >= 0; g--) {
+          for (int k = 0; k < a.c; k++) acc = oct_dbl<F>(acc, b3);
+          const Proj<F> v = load(m * a.groups_per_msm + g);
+          acc = oct_add<F>(acc, v, b3);
+        }
+        const bool inf = acc.is_inf();
+        if (a.out_xyzz) {
+          const XYZZ<F> x = oct_to_xyzz<F>(acc);
+          if (tl.lane == 0) a.out_xyzz[m] = x;
+        }
+        if (tl.lane == 0) {
+          const int nbytes = CoordCount<F>::value * a.modbytes;
+          if (!a.want_affine) {
+            a.is_inf[m] = inf ? 1 : 0;
+          } else if (inf) {
+            for (int j = 0; j < nbytes; j++) a.out_bytes[m * nbytes + j] = 0;
+            a.is_inf[m] = 1;
+          } else {
+            const F zi = F::inv(acc.Z);
+            const Affine<F> aff{F::mul(acc.X, zi), F::mul(acc.Y, zi)};
+            affine_to_bytes(aff, a.out_bytes + m * nbytes, a.modbytes);
+            a.is_inf[m] = 0;
+          }
+        }
+      }
+    }
+  }
+}
+
+}  // namespace kzgb200
+#endif

@@ -37,9 +37,12 @@ def test_tail_and_fused_sort_give_the_same_bytes(cname):
             coeffs = [rng.randrange(C.r) for _ in range(count * batch)]
             raw = C.scalars_to_bytes(coeffs)
             ctx.set_option("tail", 1)
-            got, infs = ctx.msm_g1_batch(raw, count, batch)
+            got, infs = ctx.msm_g1_batch(raw, count, batch)       # projective 8-lane tail (default)
+            ctx.set_option("tail_proj", 0)
+            assert ctx.msm_g1_batch(raw, count, batch) == (got, infs), (pre, count, batch)  # XYZZ 4-lane tail
+            ctx.set_option("tail_proj", 1)
             ctx.set_option("tail", 0)
-            old, infs0 = ctx.msm_g1_batch(raw, count, batch)
+            old, infs0 = ctx.msm_g1_batch(raw, count, batch)      # round-1 multi-launch path
             assert got == old and infs == infs0, (pre, count, batch)
             if count <= 4097:  # against the oracle through the known secret: sum c_i [s^i]G = [P(s)]G
                 want = C.g1_to_octet(C.mul(C.poly_eval(coeffs[:count], s), C.g1))[1:]
@@ -51,6 +54,9 @@ def test_tail_and_fused_sort_give_the_same_bytes(cname):
                          ("single", [0] * (nmax - 1) + [rng.randrange(1, C.r)]), ("zeros", [0] * 100)):
             raw = C.scalars_to_bytes(sc)
             got = ctx.msm_g1(raw, len(sc))
+            ctx.set_option("tail_proj", 0)
+            assert ctx.msm_g1(raw, len(sc)) == got, (pre, name)
+            ctx.set_option("tail_proj", 1)
             ctx.set_option("tail", 0)
             assert ctx.msm_g1(raw, len(sc)) == got, (pre, name)
             ctx.set_option("tail", 1)
