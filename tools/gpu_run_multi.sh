@@ -7,8 +7,8 @@ mkdir -p gpurun_out
 nvidia-smi topo -m > gpurun_out/${T}_topo.txt 2>&1
 timeout 1200 python -m pytest tests/test_gpu_tail_and_group.py -q --timeout 900 -k "group or nccl" > gpurun_out/${T}_pytest_group.log 2>&1; echo "group tests rc=$?"
 tail -15 gpurun_out/${T}_pytest_group.log
-timeout 900 python tools/gpu_probe_group.py --devices $N > gpurun_out/${T}_probe_group.json 2> gpurun_out/${T}_probe_group.err; echo "probe group rc=$?"
-cat gpurun_out/${T}_probe_group.json
+timeout 900 python bench.py --single-process --gpus $N --steps 5 > gpurun_out/${T}_bench_single_process_n${N}.json 2> gpurun_out/${T}_bench_single_process_n${N}.err; echo "single-process rc=$?"
+cat gpurun_out/${T}_bench_single_process_n${N}.json
 timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 10 --warmup 3 --no-cpu > gpurun_out/${T}_bench_n${N}.json 2> gpurun_out/${T}_bench_n${N}.err; echo "bench rc=$?"
 tail -c 800 gpurun_out/${T}_bench_n${N}.err
 python - <<PY
