@@ -140,9 +140,9 @@ __device__ __noinline__ XYZZ<F> oct_to_xyzz(const Proj<F>& a) {
 
 template <class F>
 __device__ Proj<F> oct_small_mul(const Proj<F>& p, uint32_t k, int b3) {
-  Proj<F> m{F::zero(), F::one(), F::zero()};
-  if (k == 0) return m;
-  for (int bit = top_bit_u32(k); bit >= 0; bit--) {
+  if (k == 0) return Proj<F>{F::zero(), F::one(), F::zero()};
+  Proj<F> m = p;  // the top bit
+  for (int bit = top_bit_u32(k) - 1; bit >= 0; bit--) {
     m = oct_dbl<F>(m, b3);
     if ((k >> bit) & 1) m = oct_add<F>(m, p, b3);
   }
@@ -365,9 +365,14 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, 
         }
         for (int k = 0; k < a.h; k++) acc = oct_dbl<F>(acc, b3);
         acc = oct_add<F>(acc, b, b3);
-        if (ol.lead) gout[g] = acc;
+        if (a.last_stage >= TAIL_FINISH) {
+          if (ol.lead) gout[g] = acc;
+        } else {  // a separate msm_finish launch follows (large batches): it reads XYZZ
+          const XYZZ<F> x = oct_to_xyzz<F>(acc);
+          if (ol.lead) a.group_out[g] = x;
+        }
       }
-      group_xyzz = false;
+      group_xyzz = a.last_stage < TAIL_FINISH;
     } else {
       for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads()) msm_group_combine_thread<F>(a.h, rin.p, cin.p, a.group_out, g);
     }
