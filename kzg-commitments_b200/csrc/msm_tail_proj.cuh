@@ -14,7 +14,8 @@
 // msm_tail_proj is msm_tail (msm_tail.cuh) with these operations for every step that is narrow enough for the
 // 8-lane teams; the fold of the task partials (in place on the XYZZ partials that the wide kernels also read) and
 // levels of more than 4 rounds of teams keep XYZZ, converted on first use (X ZZZ : Y ZZ : ZZ ZZZ, one round).
-// G2 keeps msm_tail: its 3b' is a general Fp2 element on the D-type twists.
+// G2 runs through the same kernel over Fp2: the twist constants are tiny too (b' = 5 + 5i, 1 - i, 4 + 4i), and an
+// Fp2 product being three dependent Fp products, cutting five rounds to two matters three times as much there.
 #pragma once
 #include "msm_tail.cuh"
 
@@ -38,9 +39,15 @@ struct Octet {
   }
 };
 
-// k * x for a small positive k (3b <= 15) by doubling and adding
+// 3b of the curve equation as small integers: 3b for G1 (re), 3b' = re + im i for the twist (G2); all three curve
+// configurations have tiny constants here (b = 5, 2, 4; b' = 5 + 5i, 1 - i, 4 + 4i), so the products are additions.
+struct B3 {
+  int re, im;
+};
+
+// k * x for a small non-zero k by doubling and adding
 template <class F>
-__device__ __forceinline__ F mul_small(const F& x, int k) {
+__device__ __forceinline__ F mul_small_pos(const F& x, int k) {
   F r = x;
   int bit = 31 - __clz(k);
   for (bit--; bit >= 0; bit--) {
@@ -49,10 +56,26 @@ __device__ __forceinline__ F mul_small(const F& x, int k) {
   }
   return r;
 }
+template <class P>
+__device__ __forceinline__ Field<P> mul_small(const Field<P>& x, B3 k) {
+  return mul_small_pos(x, k.re);
+}
+// (a + b i)(re + im i) = (a re - b im) + (a im + b re) i
+template <class P>
+__device__ __forceinline__ Field2<P> mul_small(const Field2<P>& x, B3 k) {
+  using Base = Field<P>;
+  const int are = k.re < 0 ? -k.re : k.re, aim = k.im < 0 ? -k.im : k.im;
+  Base a_re = mul_small_pos(x.a, are), b_re = mul_small_pos(x.b, are);
+  if (k.re < 0) { a_re = Base::neg(a_re); b_re = Base::neg(b_re); }
+  if (k.im == 0) return Field2<P>{a_re, b_re};
+  Base a_im = mul_small_pos(x.a, aim), b_im = mul_small_pos(x.b, aim);
+  if (k.im < 0) { a_im = Base::neg(a_im); b_im = Base::neg(b_im); }
+  return Field2<P>{Base::sub(a_re, b_im), Base::add(a_im, b_re)};
+}
 
 // a + b, complete (RCB Algorithm 7 with a = 0, b3 = 3b).  a, b and the result are replicated on the 8 lanes.
 template <class F>
-__device__ __noinline__ Proj<F> oct_add(const Proj<F>& a, const Proj<F>& b, int b3) {
+__device__ __noinline__ Proj<F> oct_add(const Proj<F>& a, const Proj<F>& b, B3 b3) {
   const Octet tm;
   const int r = tm.role, base = tm.base;
   const unsigned mask = tm.mask;
@@ -84,7 +107,7 @@ __device__ __noinline__ Proj<F> oct_add(const Proj<F>& a, const Proj<F>& b, int 
 
 // 2 a, complete (RCB Algorithm 9 with a = 0)
 template <class F>
-__device__ __noinline__ Proj<F> oct_dbl(const Proj<F>& a, int b3) {
+__device__ __noinline__ Proj<F> oct_dbl(const Proj<F>& a, B3 b3) {
   const Octet tm;
   const int r = tm.role, base = tm.base;
   const unsigned mask = tm.mask;
@@ -139,7 +162,7 @@ __device__ __noinline__ XYZZ<F> oct_to_xyzz(const Proj<F>& a) {
 }
 
 template <class F>
-__device__ Proj<F> oct_small_mul(const Proj<F>& p, uint32_t k, int b3) {
+__device__ Proj<F> oct_small_mul(const Proj<F>& p, uint32_t k, B3 b3) {
   if (k == 0) return Proj<F>{F::zero(), F::one(), F::zero()};
   Proj<F> m = p;  // the top bit
   for (int bit = top_bit_u32(k) - 1; bit >= 0; bit--) {
@@ -184,7 +207,7 @@ struct OctLane {
 // one level of the two pairwise trees; switches an array to projective the first time its level fits the teams
 template <class F>
 __device__ __forceinline__ void tailp_pair_level(const TailLane& tl, const OctLane& ol, MixedArray<F>& in0, MixedArray<F>& out0,
-                                                 uint64_t n0, MixedArray<F>& in1, MixedArray<F>& out1, uint64_t n1, int b3) {
+                                                 uint64_t n0, MixedArray<F>& in1, MixedArray<F>& out1, uint64_t n1, B3 b3) {
   const bool octs = ol.fits(n0 + n1) || (n0 && !in0.xyzz) || (n1 && !in1.xyzz);
   if (octs) {
     for (uint64_t t = ol.oct; t < n0 + n1; t += ol.nocts) {
@@ -214,7 +237,7 @@ __device__ __forceinline__ void tailp_pair_level(const TailLane& tl, const OctLa
 template <class F>
 __device__ __forceinline__ void tailp_trees(const TailLane& tl, const OctLane& ol, GridBarrier* bar, MixedArray<F>& in0,
                                             MixedArray<F>& out0, uint64_t sums0, uint64_t& len0, MixedArray<F>& in1,
-                                            MixedArray<F>& out1, uint64_t sums1, uint64_t& len1, int b3) {
+                                            MixedArray<F>& out1, uint64_t sums1, uint64_t& len1, B3 b3) {
   while (len0 > 1 || len1 > 1) {
     tailp_pair_level<F>(tl, ol, in0, out0, len0 > 1 ? sums0 * (len0 / 2) : 0, in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0, b3);
     if (len0 > 1) { MixedArray<F> t = in0; in0 = out0; out0 = t; len0 /= 2; }
@@ -224,7 +247,7 @@ __device__ __forceinline__ void tailp_trees(const TailLane& tl, const OctLane& o
 }
 
 template <class F>
-__global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, int b3) {
+__global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, B3 b3) {
   const TailLane tl;
   const OctLane ol(tl);
   const bool lead4 = (threadIdx.x & 3) == 0;
