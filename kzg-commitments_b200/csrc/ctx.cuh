@@ -410,7 +410,8 @@ struct Ctx final : kzg_gpu_ctx {
   int prepare_tail() {
     if (tail_ready[std::is_same<F, Fp2>::value ? 1 : 0]) return ensure_barrier();
     CK(cudaFuncSetAttribute(msm_tail<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(msm_tail_proj<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
+    if constexpr (std::is_same<F, Fp>::value)
+      CK(cudaFuncSetAttribute(msm_tail_proj<Fp>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
     int rcb = ensure_barrier();
     if (rcb) return rcb;
     tail_ready[std::is_same<F, Fp2>::value ? 1 : 0] = true;
@@ -625,9 +626,14 @@ struct Ctx final : kzg_gpu_ctx {
       ta.rin = rin; ta.rout = rout; ta.cin = cin; ta.cout = cout;
       ta.r_len = r_len; ta.c_len = c_len;
       (void)items;  // always one CTA per SM: narrow levels are dealt out one warp per SM first (msm_tail.cuh)
-      if (opt_tail_proj) {  // complete projective formulas on 8-lane teams, two product rounds per addition
-        B3 b3 = std::is_same<F, Fp>::value ? B3{3 * C::G1_B, 0} : B3{3 * C::G2_B_RE, 3 * C::G2_B_IM};
-        return launch_cooperative((const void*)msm_tail_proj<F>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES, &b3);
+      // G1: complete projective formulas on 8-lane teams, two product rounds per addition.  G2 was measured both ways
+      // (profiles/r2k_probe_g2.json: 1.24 vs 1.23 ms at 4097 terms — over Fp2 the replicated linear steps and the
+      // register spills of the 8-lane form eat what the shorter product chain saves), so it keeps the XYZZ teams.
+      if constexpr (std::is_same<F, Fp>::value) {
+        if (opt_tail_proj) {
+          B3 b3{3 * C::G1_B, 0};
+          return launch_cooperative((const void*)msm_tail_proj<Fp>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES, &b3);
+        }
       }
       return launch_cooperative((const void*)msm_tail<F>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES);
     };

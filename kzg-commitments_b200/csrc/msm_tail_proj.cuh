@@ -14,8 +14,9 @@
 // msm_tail_proj is msm_tail (msm_tail.cuh) with these operations for every step that is narrow enough for the
 // 8-lane teams; the fold of the task partials (in place on the XYZZ partials that the wide kernels also read) and
 // levels of more than 4 rounds of teams keep XYZZ, converted on first use (X ZZZ : Y ZZ : ZZ ZZZ, one round).
-// G2 runs through the same kernel over Fp2: the twist constants are tiny too (b' = 5 + 5i, 1 - i, 4 + 4i), and an
-// Fp2 product being three dependent Fp products, cutting five rounds to two matters three times as much there.
+// The code is generic over Fp2 as well (the twist constants are tiny too: b' = 5 + 5i, 1 - i, 4 + 4i) and was measured
+// for G2 (profiles/r2k_probe_g2.json): no gain — 255 registers with spills and twice the linear work per step — so
+// ctx.cuh instantiates it for G1 only and G2 keeps msm_tail.
 #pragma once
 #include "msm_tail.cuh"
 
