@@ -34,7 +34,7 @@ def main():
         raw = random_scalars(8192, 5).view(np.uint8).tobytes()
         for _ in range(a.reps):
             ctx.poly_quotient(raw, 0, 4096)
-    elif a.what in ("msm20", "msm12", "msm16"):
+    elif a.what.startswith("msm"):
         n = 1 << int(a.what[3:])
         ctx.set_option("setup_g2", 0)
         ctx.set_option("precompute", 1)
