@@ -593,9 +593,7 @@ struct Ctx final : kzg_gpu_ctx {
     }
     phase_mark(1);
     {
-      // at most one resident wave of CTAs; the kernel deals further rounds of tasks out itself (snake order)
-      const int resident = max_cooperative_blocks((const void*)msm_accumulate<F>, 128);
-      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)std::max(resident, 148));
+      unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)1 << 30);
       const size_t pt_stride = (precomp && std::is_same<F, Fp>::value && levels == 0) ? g1_point_stride : sizeof(Affine<F>);
       msm_accumulate<F><<<grid, 128, 0, stream>>>(task_first.as<uint32_t>() + nbuckets, tasks.as<MsmTask>(), seg_sorted,
                                                   seg_pts, partial.as<XYZZ<F>>(), pt_stride);

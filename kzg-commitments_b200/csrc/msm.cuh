@@ -405,18 +405,9 @@ __global__ void __launch_bounds__(128, sizeof(F) <= 48 ? 4 : 1)
 msm_accumulate(const uint32_t* __restrict__ ntasks_ptr, const MsmTask* __restrict__ tasks,
                const uint32_t* __restrict__ sorted, const Affine<F>* __restrict__ bases, XYZZ<F>* __restrict__ partial,
                size_t point_stride) {
-  // The grid is at most one resident wave (ctx.cuh).  Tasks are ordered by descending length, so a thread that takes
-  // tasks t, t + N, t + 2N, ... would get the longest of every round; dealing the rounds out in SNAKE order
-  // (t, 2N-1-t, 2N+t, ...) pairs long with short.  With one task per thread and 1.3 waves of CTAs the kernel ran the
-  // short tail of the list on a third of the machine (ncu, 2^16..2^18 points: multiplier pipe 76-78 % busy against
-  // 93.8 % at 2^20, profiles/r2m_*).
   const uint32_t ntasks = *ntasks_ptr;
-  const uint32_t N = gridDim.x * blockDim.x, t = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t round = 0;
-  for (uint32_t base = 0; base < ntasks; base += N, round++) {
-    const uint32_t i = base + ((round & 1u) ? N - 1u - t : t);
-    if (i < ntasks) msm_accumulate_thread<F>(tasks, sorted, bases, partial, i, point_stride);
-  }
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ntasks; i += gridDim.x * blockDim.x)
+    msm_accumulate_thread<F>(tasks, sorted, bases, partial, i, point_stride);
 }
 // Device fold: a segmented binary tree over the flat array of task partials, one launch per level.
 // At level l the partial of task k (k a multiple of 2^(l+1)) absorbs that of task k + 2^l of the same
