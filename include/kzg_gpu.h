@@ -183,6 +183,21 @@ int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops_per_second);
  * failed checks in *failures. */
 int kzg_gpu_selftest(kzg_gpu_ctx* ctx, int* failures);
 
+/* kzg_gpu_poly_eval_range for callers that CANNOT ALLOCATE (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * Same values as kzg_gpu_poly_eval_range (y_j = P(first_root + j), j < k), but d_coeffs (n*SB bytes) and d_y_out (k*SB
+ * bytes) are DEVICE buffers of the caller, the call makes no cudaMalloc / cudaFree / allocating library call, and its
+ * scratch is one fixed 4 MiB static __device__ array (held by every GPU that loads the library, until exit).
+ * n > KZG_GPU_NOALLOC_MAX_COEFFS or k > KZG_GPU_NOALLOC_MAX_POINTS -> KZG_GPU_ERR_ARG with a message in kzg_gpu_last_error.
+ * The work is enqueued on the context's stream (kzg_gpu_ctx_stream) and the call returns without waiting.  All calls on
+ * one GPU share the scratch array (it keeps the last call's contents; nothing in it needs to start at zero): calls that
+ * overlap on the GPU race — serialise them.  Make the first call per device before starting a graph capture (it looks
+ * the array's address up and loads the kernels). */
+#define KZG_GPU_NOALLOC_MAX_COEFFS 65536
+#define KZG_GPU_NOALLOC_MAX_POINTS 65536
+int kzg_gpu_poly_eval_range_noalloc(kzg_gpu_ctx* ctx, const void* d_coeffs, uint64_t n, int64_t first_root, uint64_t k,
+                                    void* d_y_out);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Multi-GPU: a GROUP of devices of one box behind the same C ABI (SURVEY.md 8(b) "devices, n_devices" and 8(e)).
  *

@@ -68,6 +68,7 @@ def load_library():
         "kzg_gpu_g1_sum_partials_device": (ctypes.c_int, [vp, vp, u64, u8p, ip]),
         "kzg_gpu_poly_quotient": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
         "kzg_gpu_poly_eval_range": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p]),
+        "kzg_gpu_poly_eval_range_noalloc": (ctypes.c_int, [vp, vp, u64, i64, u64, vp]),
         "kzg_gpu_prove": (ctypes.c_int, [vp, u8p, u64, i64, u64, u8p, ip]),
         "kzg_gpu_interpolate_range": (ctypes.c_int, [vp, u8p, i64, u64, u8p, u8p]),
         "kzg_gpu_commit_bytes": (ctypes.c_int, [vp, vp, u64, ctypes.c_int, i64, u8p, u8p, ctypes.POINTER(ctypes.c_int)]),
@@ -107,6 +108,7 @@ EXPORTED_SYMBOLS = [
     "kzg_gpu_prove", "kzg_gpu_ctx_stream", "kzg_gpu_launch_count", "kzg_gpu_microbench", "kzg_gpu_selftest",
     "kzg_gpu_phase_times", "kzg_gpu_msm_stats", "kzg_gpu_msm_partial_device", "kzg_gpu_g1_sum_partials_device",
     "kzg_gpu_interpolate_range", "kzg_gpu_prove_batch", "kzg_gpu_commit_bytes", "kzg_gpu_setup_powers_range",
+    "kzg_gpu_poly_eval_range_noalloc",
     "kzg_gpu_device_count", "kzg_gpu_group_create", "kzg_gpu_group_destroy", "kzg_gpu_group_size", "kzg_gpu_group_ctx",
     "kzg_gpu_group_last_error", "kzg_gpu_group_set_option", "kzg_gpu_group_srs_load", "kzg_gpu_group_setup_powers",
     "kzg_gpu_group_msm_g1", "kzg_gpu_group_msm_g1_batch", "kzg_gpu_group_prove_batch",
@@ -250,6 +252,12 @@ class Context:
         out = ctypes.create_string_buffer(k * self.SB)
         self._check(self.lib.kzg_gpu_poly_eval_range(self.h, coeffs, n, first_root, k, out), "poly_eval_range")
         return out.raw
+
+    def poly_eval_range_noalloc(self, d_coeffs, n, first_root, k, d_y_out):
+        """kzg_gpu_poly_eval_range_noalloc: DEVICE buffers in and out (tensors or addresses), nothing allocated, enqueued
+        on the context's stream without waiting."""
+        self._check(self.lib.kzg_gpu_poly_eval_range_noalloc(self.h, _ptr(d_coeffs), n, first_root, k, _ptr(d_y_out)),
+                    "poly_eval_range_noalloc")
 
     def interpolate_range(self, ys, first_x, want_vanishing=True):
         """(I, Z) through the nodes first_x + i: I as k coefficient records, Z as k + 1 (or None)."""
