@@ -175,7 +175,8 @@ int kzg_gpu_msm_stats(kzg_gpu_ctx* ctx, uint64_t* out, int n);
  * kind 3: Fr Montgomery products/s
  * kinds 4..7: LATENCY probes in the configuration of the reduction tail (one CTA of 128 threads per SM), returned as
  * steps per second of ONE dependent chain: 4 = grid barriers, 5 = 4-lane team additions (XYZZ, G1 field),
- * 6 = single-thread additions, 7 = dependent Fp Montgomery products */
+ * 6 = single-thread additions, 7 = dependent Fp Montgomery products, 8 = Fp inversions (batched divsteps),
+ * 9 = Fp inversions by the binary extended GCD of round 1 (kept as a cross-check) */
 int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops_per_second);
 
 /* Device self-test: field, Fp2 and group-law identities on random inputs, compared on device against

@@ -1379,7 +1379,7 @@ struct Ctx final : kzg_gpu_ctx {
   int microbench(int kind, double* ops) override {
     std::lock_guard<std::recursive_mutex> lock(mu);
     CK(cudaSetDevice(device));
-    if (!ops || kind < 0 || kind > 7) return KZG_GPU_ERR_ARG;
+    if (!ops || kind < 0 || kind > 9) return KZG_GPU_ERR_ARG;
     CK(scal.ensure(64));
     if (kind >= 4) return microbench_latency(kind, ops);
     const int blocks = 148 * 8, threads = 256;
@@ -1418,7 +1418,7 @@ struct Ctx final : kzg_gpu_ctx {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    const int iters = kind == 4 ? 2000 : kind == 7 ? 4000 : 400;
+    const int iters = kind == 4 ? 2000 : kind == 7 ? 4000 : kind >= 8 ? 50 : 400;
     float best = 1e30f;
     for (int rep = 0; rep < 3; rep++) {
       CK(cudaEventRecord(e0, stream));

@@ -106,7 +106,8 @@ KZG_HDN int check_field(Lcg& g) {
   bad += !(F::add(a, F::neg(a)).is_zero());
   bad += !(F::to_mont(F::from_mont(a)) == a);
   if (!a.is_zero()) bad += !(F::mul(a, F::inv(a)) == F::one());
-  bad += !(F::inv(a) == F::inv_fermat(a));  // binary-GCD inverse against the Fermat ladder
+  bad += !(F::inv(a) == F::inv_fermat(a));  // divstep (safegcd) inverse against the Fermat ladder
+  bad += !(F::inv(a) == F::inv_bingcd(a));  // ... and against the binary extended GCD
   // the Karatsuba / separated-reduction product (field.cuh, KZG_KARATSUBA) against the interleaved one
   if constexpr (F::L % 4 == 0) {
     const F m1 = F::neg(F::one());

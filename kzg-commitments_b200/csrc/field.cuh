@@ -306,12 +306,153 @@ struct alignas((P::L % 4 == 0) ? 16 : 8) Field {  // aligned for 128-bit (64-bit
     return mul(a, o);
   }
 
-  // Inverse by the binary extended Euclidean algorithm on the raw limbs (shifts, adds, compares: no
-  // multiplications, ~2*BITS short iterations) followed by two Montgomery products to restore the
-  // R factor.  A single thread's Fermat ladder is ~1.5*BITS dependent modmuls (0.65 ms for BLS12-381 Fp,
-  // profiles/r1c); this is several times shorter, which matters because the MSM finish is ONE inversion
-  // on ONE thread.  Variable time (the inputs here are public group elements).  inv(0) = 0.
+  // ---- Inverse by BATCHED DIVSTEPS ("safegcd", Bernstein-Yang 2019, in the 30-bit-limb variable-time form that
+  // libsecp256k1's modinv32 popularised): f = p, g = a; 30 division steps at a time are run on the low words only and
+  // collected in a 2x2 integer matrix t, which is then applied to the full-length (f, g) — exact division by 2^30 —
+  // and to (d, e) modulo p, with d a = f, e a = g (mod p) throughout.  When g reaches 0, f = +-1 and a^-1 = +-d.
+  // About 27 batches of ~560 native 32-bit instructions for BLS12-381 Fp (12 for BN158) against ~760 iterations of
+  // multi-limb shifts / adds / compares for the binary GCD it replaces (kept below as inv_bingcd, the cross-check):
+  // the single inversion at the end of every MSM was 90 us = 17 % of a degree-4096 commitment (profiles/r2_tail.md),
+  // and the same routine sits in the setup normalisation and the window-table builds.
+  // Variable time (the inputs are public group elements).  inv(0) = 0.  Limbs are 30-bit, the top one signed.
+  static constexpr int N30 = (P::BITS + 2 + 29) / 30;
+  KZG_HD static constexpr uint32_t mod_limb30(int i) {  // bits [30 i, 30 i + 30) of the modulus
+    return (uint32_t)((((30 * i) / 32 < L ? (uint64_t)P::mod((30 * i) / 32 < L ? (30 * i) / 32 : 0) : 0ull) |
+                       ((30 * i) / 32 + 1 < L ? (uint64_t)P::mod((30 * i) / 32 + 1 < L ? (30 * i) / 32 + 1 : 0) << 32 : 0ull)) >>
+                      ((30 * i) % 32)) & 0x3fffffffu;
+  }
+  KZG_HD static int ctz_u32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+  }
   KZG_HDN static Field inv(const Field& a) {
+    if (a.is_zero()) return zero();
+    constexpr int N = N30;
+    constexpr int32_t M30 = 0x3fffffff;
+    constexpr uint32_t minv30 = (0u - P::INV) & 0x3fffffffu;  // p^-1 mod 2^30  (P::INV = -p^-1 mod 2^32)
+    constexpr int MAX_BATCHES = (49 * P::BITS + 80) / 17 / 30 + 2;  // proven bound on the number of division steps
+    int32_t f[N], g[N], d[N], e[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+      const int w = (30 * i) >> 5, sh = (30 * i) & 31;
+      uint64_t x = w < L ? (uint64_t)a.v[w < L ? w : 0] : 0ull;
+      if (w + 1 < L) x |= (uint64_t)a.v[w + 1 < L ? w + 1 : 0] << 32;
+      g[i] = (int32_t)((uint32_t)(x >> sh) & 0x3fffffffu);
+      f[i] = (int32_t)mod_limb30(i);
+      d[i] = 0;
+      e[i] = 0;
+    }
+    e[0] = 1;
+    int32_t eta = -1;
+    for (int batch = 0; batch < MAX_BATCHES; batch++) {
+      // 30 division steps on the low 32 bits of f and g; t = [u v; q r]
+      uint32_t u = 1, v = 0, q = 0, r = 1;
+      uint32_t fl = (uint32_t)f[0] | ((uint32_t)f[1] << 30), gl = (uint32_t)g[0] | ((uint32_t)g[1] << 30);
+      int i = 30;
+      for (;;) {
+        const int zeros = ctz_u32(gl | (0xffffffffu << i));  // a sentinel bit stops the count at i
+        gl >>= zeros; u <<= zeros; v <<= zeros; eta -= zeros; i -= zeros;
+        if (i == 0) break;
+        if (eta < 0) {
+          eta = -eta;
+          uint32_t t = fl; fl = gl; gl = 0u - t;
+          t = u; u = q; q = 0u - t;
+          t = v; v = r; r = 0u - t;
+        }
+        // f and g are odd: add the multiple w of f that clears the low min(eta + 1, i, 4) bits of g
+        const int limit = (eta + 1) > i ? i : (eta + 1);
+        const uint32_t m = (0xffffffffu >> (32 - limit)) & 15u;
+        uint32_t w = fl + (((fl + 1u) & 4u) << 1);  // f^-1 mod 16
+        w = (0u - w * gl) & m;
+        gl += fl * w; q += u * w; r += v * w;
+      }
+      const int32_t tu = (int32_t)u, tv = (int32_t)v, tq = (int32_t)q, tr = (int32_t)r;
+      // (d, e) <- t (d, e) / 2^30 mod p: a multiple of p is added so that the division is exact
+      {
+        const int32_t sd = d[N - 1] >> 31, se = e[N - 1] >> 31;
+        int32_t md = (tu & sd) + (tv & se), me = (tq & sd) + (tr & se);
+        int64_t cd = (int64_t)tu * d[0] + (int64_t)tv * e[0], ce = (int64_t)tq * d[0] + (int64_t)tr * e[0];
+        md -= (int32_t)((minv30 * (uint32_t)cd + (uint32_t)md) & (uint32_t)M30);
+        me -= (int32_t)((minv30 * (uint32_t)ce + (uint32_t)me) & (uint32_t)M30);
+        cd += (int64_t)(int32_t)mod_limb30(0) * md;
+        ce += (int64_t)(int32_t)mod_limb30(0) * me;
+        cd >>= 30;
+        ce >>= 30;
+#pragma unroll
+        for (int k = 1; k < N; k++) {
+          cd += (int64_t)tu * d[k] + (int64_t)tv * e[k] + (int64_t)(int32_t)mod_limb30(k) * md;
+          ce += (int64_t)tq * d[k] + (int64_t)tr * e[k] + (int64_t)(int32_t)mod_limb30(k) * me;
+          d[k - 1] = (int32_t)cd & M30; cd >>= 30;
+          e[k - 1] = (int32_t)ce & M30; ce >>= 30;
+        }
+        d[N - 1] = (int32_t)cd;
+        e[N - 1] = (int32_t)ce;
+      }
+      // (f, g) <- t (f, g) / 2^30, exact
+      {
+        int64_t cf = (int64_t)tu * f[0] + (int64_t)tv * g[0], cg = (int64_t)tq * f[0] + (int64_t)tr * g[0];
+        cf >>= 30;
+        cg >>= 30;
+        int32_t nz = 0;
+#pragma unroll
+        for (int k = 1; k < N; k++) {
+          cf += (int64_t)tu * f[k] + (int64_t)tv * g[k];
+          cg += (int64_t)tq * f[k] + (int64_t)tr * g[k];
+          f[k - 1] = (int32_t)cf & M30; cf >>= 30;
+          g[k - 1] = (int32_t)cg & M30; cg >>= 30;
+          nz |= g[k - 1];
+        }
+        f[N - 1] = (int32_t)cf;
+        g[N - 1] = (int32_t)cg;
+        nz |= g[N - 1];
+        if (nz == 0) break;
+      }
+    }
+    // f = +-1 and d a = f (mod p), d in (-2p, p): a^-1 = sign(f) d, brought into [0, p)
+    if (f[N - 1] < 0) {
+      int32_t c = 0;
+#pragma unroll
+      for (int k = 0; k < N - 1; k++) { const int32_t t = c - d[k]; d[k] = t & M30; c = t >> 30; }
+      d[N - 1] = c - d[N - 1];
+    }
+    for (int pass = 0; pass < 2; pass++) {  // + p while negative (at most twice)
+      if (d[N - 1] < 0) {
+        int32_t c = 0;
+#pragma unroll
+        for (int k = 0; k < N - 1; k++) { const int32_t t = d[k] + (int32_t)mod_limb30(k) + c; d[k] = t & M30; c = t >> 30; }
+        d[N - 1] += (int32_t)mod_limb30(N - 1) + c;
+      }
+    }
+    {  // - p if that stays non-negative
+      int32_t t[N], c = 0;
+#pragma unroll
+      for (int k = 0; k < N - 1; k++) { const int32_t x = d[k] - (int32_t)mod_limb30(k) + c; t[k] = x & M30; c = x >> 30; }
+      t[N - 1] = d[N - 1] - (int32_t)mod_limb30(N - 1) + c;
+      if (t[N - 1] >= 0) {
+#pragma unroll
+        for (int k = 0; k < N; k++) d[k] = t[k];
+      }
+    }
+    Field res;
+#pragma unroll
+    for (int j = 0; j < L; j++) {  // 30-bit limbs -> 32-bit words
+      const int k = (32 * j) / 30, sh = (32 * j) % 30;
+      uint32_t x = k < N ? (uint32_t)d[k < N ? k : 0] >> sh : 0u;
+      if (k + 1 < N) x |= (uint32_t)d[k + 1 < N ? k + 1 : 0] << (30 - sh);
+      if (k + 2 < N && 60 - sh < 32) x |= (uint32_t)d[k + 2 < N ? k + 2 : 0] << (60 - sh);
+      res.v[j] = x;
+    }
+    // res = (aR)^-1 as a plain residue; two products by R^2 give a^-1 * R
+    res = mul(res, r2());
+    return mul(res, r2());
+  }
+
+  // The binary extended Euclidean algorithm on the raw limbs (shifts, adds, compares; ~2*BITS short iterations): the
+  // inversion of round 1, kept as an independent formulation for the self-tests.
+  KZG_HDN static Field inv_bingcd(const Field& a) {
     if (a.is_zero()) return zero();
     uint32_t u[L], w[L], x1[L], x2[L];
 #pragma unroll

@@ -358,6 +358,8 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) bench_latency_chain(int kind,
   for (int it = 0; it < iters; it++) {
     if (kind == 5) acc = team_add<F>(acc, p);   // 4 lanes per addition: 5 product rounds
     else if (kind == 6) acc.add(p);             // one thread per addition: 14 dependent products
+    else if (kind == 8) m = F::inv(F::add(m, p.X));  // one field inversion (divsteps) per step
+    else if (kind == 9) m = F::inv_bingcd(F::add(m, p.X));  // the binary GCD it replaced
     else m = F::mul(m, p.X);                    // kind 7: one dependent Montgomery product
   }
   uint32_t o = 0;

@@ -57,7 +57,7 @@ def test_montgomery_field_ops(hc, cname):
             for op, want in ((0, a * b % mod), (1, (a + b) % mod), (2, (a - b) % mod), (4, -a % mod)):
                 assert hc.hc_field_op(C.id, which, op, _words(a, n), _words(b, n), out) == 0
                 assert _val(out) == want, (cname, which, op, hex(a), hex(b))
-        for a in vals[:12]:
+        for a in vals:
             out = (ctypes.c_uint32 * n)()
             hc.hc_field_op(C.id, which, 3, _words(a, n), _words(0, n), out)
             assert _val(out) == (pow(a, -1, mod) if a else 0)

@@ -21,7 +21,7 @@ out = {"us_per_step": {}, "msm_ms": {}}
 for sleep in (0, 20, 64, 200, 1000):
     ctx.set_option("barrier_sleep", sleep)
     out["us_per_step"]["grid_barrier_sleep%d" % sleep] = 1e6 / ctx.microbench(4)
-for kind, name in ((5, "team_add"), (6, "thread_add"), (7, "fp_modmul")):
+for kind, name in ((5, "team_add"), (6, "thread_add"), (7, "fp_modmul"), (8, "fp_inv_divsteps"), (9, "fp_inv_bingcd")):
     out["us_per_step"][name] = 1e6 / ctx.microbench(kind)
 for lg in (12, 16):
     n = 1 << lg
