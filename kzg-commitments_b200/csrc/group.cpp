@@ -152,13 +152,13 @@ int kzg_gpu_group_create(kzg_gpu_group** out, int curve, const int* devices, int
   g->slice.assign(devs.size(), nullptr);
   g->slice_lo.assign(devs.size(), 0);
   g->slice_n.assign(devs.size(), 0);
-  for (size_t i = 0; i < devs.size(); i++) {
-    int rc = kzg_gpu_ctx_create(&g->full[i], curve, devs[i]);
-    if (rc) {
-      kzg_gpu_group_destroy(g);
-      return rc;
-    }
-    g->workers.push_back(i == 0 ? nullptr : new Worker());
+  // one context per device, created side by side on the worker threads: a CUDA context plus this library's module
+  // costs 0.3-1 s per device, which a process that runs ONE operation (the reference's demo CLI) would pay serially
+  for (size_t i = 0; i < devs.size(); i++) g->workers.push_back(i == 0 ? nullptr : new Worker());
+  const int rc_create = g->for_all([&](int i) -> int { return kzg_gpu_ctx_create(&g->full[i], curve, devs[i]); });
+  if (rc_create) {
+    kzg_gpu_group_destroy(g);
+    return rc_create;
   }
   *out = g;
   return KZG_GPU_OK;

@@ -165,14 +165,18 @@ size_t cache_capacity() {
   const long v = e ? atol(e) : 0;
   return v >= 1 ? (size_t)v : 8;
 }
-// how many devices a setup of n points is made resident on: all of them when a single commitment is large enough to be
-// split by point range (kzg_gpu_group_msm_g1), one otherwise; KZG_GPU_DEVICES overrides
+// how many devices a setup of n points is made resident on: all of them when a single commitment is large enough for
+// a split by point range to pay (kzg_gpu_group_msm_g1), one otherwise; KZG_GPU_DEVICES overrides
 int devices_for(size_t n) {
   const int visible = kzg_gpu_device_count();
   if (visible <= 0) return 0;
   const char* e = getenv("KZG_GPU_DEVICES");
   if (e && atoi(e) >= 1) return std::min(atoi(e), visible);
-  return n >= 65536 ? visible : 1;
+  // One device below 2^20 points: a commitment over fewer points takes under ~4 ms, and every further device costs
+  // a process 0.3-1 s of context creation (measured on 2 GPUs with the reference's one-operation-per-process demo
+  // CLI at 65536 points: the whole drop-in test file 150 s -> 373 s).  From 2^20 points on a single create_commit
+  // is split by point range over all visible devices (kzg_gpu_group_msm_g1: 3.6x on 8 GPUs at 2^20, 6.4x at 2^22).
+  return n >= ((size_t)1 << 20) ? visible : 1;
 }
 Digest digest_of(const std::vector<uint8_t>& b1, const std::vector<uint8_t>& b2) {
   Digest d = {0xcbf29ce484222325ull, 0x84222325cbf29ce4ull};  // two FNV-1a style lanes over different strides
