@@ -259,7 +259,7 @@ struct Ctx final : kzg_gpu_ctx {
     g1_point_stride = opt_table_pad && sizeof(Affine<Fp>) <= 128 ? 128 : sizeof(Affine<Fp>);
     CK(g1_table.ensure((size_t)W * srs_n * g1_point_stride));
     if (srs_n <= TABLE_TEAM_MAX_POINTS)  // latency-bound build: four lanes per point (setup.cuh)
-      msm_precompute_table_team<Fp, MAXW><<<(unsigned)((4 * srs_n + 127) / 128), 128, 0, stream>>>(
+      msm_precompute_table_team<Fp, MAXW><<<(unsigned)((TeamWidth<Fp>::LANES * srs_n + 127) / 128), 128, 0, stream>>>(
           srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>(), g1_point_stride);
     else
       msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
@@ -293,7 +293,7 @@ struct Ctx final : kzg_gpu_ctx {
     CK(cudaEventRecord(g2_table_ev, stream));          // the SRS itself was written on the main stream
     CK(cudaStreamWaitEvent(aux_stream, g2_table_ev, 0));
     if (srs_n <= TABLE_TEAM_MAX_POINTS)
-      msm_precompute_table_team<Fp2, MAXW><<<(unsigned)((4 * srs_n + 127) / 128), 128, 0, aux_stream>>>(
+      msm_precompute_table_team<Fp2, MAXW><<<(unsigned)((TeamWidth<Fp2>::LANES * srs_n + 127) / 128), 128, 0, aux_stream>>>(
           srs_n, srs_n, table_c, table_W, g2.as<Affine<Fp2>>(), g2_table.as<Affine<Fp2>>(), sizeof(Affine<Fp2>));
     else
       msm_precompute_table<Fp2, MAXW><<<(unsigned)((srs_n + 63) / 64), 64, 0, aux_stream>>>(
@@ -392,7 +392,7 @@ struct Ctx final : kzg_gpu_ctx {
       PairJob<F> j1{in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0};
       const uint64_t mx = std::max(j0.n_out, j1.n_out);
       if (opt_team && j0.n_out + j1.n_out <= TEAM_MAX_ITEMS) {  // latency-bound level: 4 lanes per addition
-        dim3 grid((unsigned)((4 * mx + 127) / 128), 2);
+        dim3 grid((unsigned)((WIDE_LANES * mx + 127) / 128), 2);
         msm_pair_sum_team<F><<<grid, 128, 0, stream>>>(j0, j1);
       } else {
         dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)148 * 64), 2);
@@ -656,7 +656,7 @@ struct Ctx final : kzg_gpu_ctx {
       int fold_levels = 0;
       while ((1ull << fold_levels) < nt_bound && fold_levels < 31) fold_levels++;
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)sms * 8);
-      unsigned grid_team = (unsigned)std::min<uint64_t>((4 * max_tasks + 127) / 128, (uint64_t)sms * 8);
+      unsigned grid_team = (unsigned)std::min<uint64_t>((WIDE_LANES * max_tasks + 127) / 128, (uint64_t)sms * 8);
       for (int l = 0; l < fold_levels; l++) {
         if (opt_team)
           msm_fold_level_team<F><<<grid_team, 128, 0, stream>>>(l, task_first.as<uint32_t>() + nbuckets, d_hist + MSM_MAX_CHUNK + 1,
@@ -678,7 +678,7 @@ struct Ctx final : kzg_gpu_ctx {
         }
         const uint64_t mx = std::max(j0.n_out, j1.n_out);
         if (opt_team && j0.n_out + j1.n_out <= TEAM_MAX_ITEMS) {  // latency-bound level: 4 lanes per addition
-          dim3 grid((unsigned)((4 * mx + 127) / 128), 2);
+          dim3 grid((unsigned)((WIDE_LANES * mx + 127) / 128), 2);
           msm_pair_sum_team<F><<<grid, 128, 0, stream>>>(j0, j1);
         } else {
           dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)148 * 64), 2);
@@ -695,7 +695,7 @@ struct Ctx final : kzg_gpu_ctx {
       BucketJob<F> jc{cin, Cn, R, 1, Cn, groups * Cn * Lc};
       const uint64_t mx = std::max(jr.total, jc.total);
       if (opt_team && jr.total + jc.total <= TEAM_MAX_ITEMS) {
-        dim3 grid((unsigned)((4 * mx + 127) / 128), 2);
+        dim3 grid((unsigned)((WIDE_LANES * mx + 127) / 128), 2);
         msm_bucket_pairs_team<F><<<grid, 128, 0, stream>>>((uint64_t)sh.nb, task_first.as<uint32_t>(), partial.as<XYZZ<F>>(), jr, jc);
       } else {
         dim3 grid((unsigned)std::min<uint64_t>((mx + 127) / 128, (uint64_t)sms * 64), 2);
@@ -717,7 +717,7 @@ struct Ctx final : kzg_gpu_ctx {
       } else {
         const uint64_t mw = std::max(wr.total, wc.total);
         if (opt_team && wr.total + wc.total <= TEAM_MAX_ITEMS) {
-          dim3 gridw((unsigned)((4 * mw + 127) / 128), 2);
+          dim3 gridw((unsigned)((WIDE_LANES * mw + 127) / 128), 2);
           msm_weighted_chunks_team<F><<<gridw, 128, 0, stream>>>(wr, wc);
         } else {
           dim3 gridw((unsigned)std::min<uint64_t>((mw + 127) / 128, (uint64_t)sms * 64), 2);
@@ -739,7 +739,7 @@ struct Ctx final : kzg_gpu_ctx {
         if (rc) return rc;
       } else {
         if (opt_team && groups <= TEAM_MAX_ITEMS)
-          msm_group_combine_team<F><<<(unsigned)((4 * groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
+          msm_group_combine_team<F><<<(unsigned)((WIDE_LANES * groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
         else
           msm_group_combine<F><<<(unsigned)((groups + 127) / 128), 128, 0, stream>>>(groups, h, t1, t2, group_out.as<XYZZ<F>>());
         LAUNCHED();
@@ -749,7 +749,7 @@ struct Ctx final : kzg_gpu_ctx {
     if (in_tail && finish_in_tail) {
       // Horner over the windows, affine normalisation and bytes ran at the end of the tail kernel
     } else if (opt_team && sh.groups_per_msm > 1 && batch <= TEAM_MAX_ITEMS)  // Horner over the windows: a long dependent chain
-      msm_finish_team<F><<<(unsigned)((4 * batch + 127) / 128), 128, 0, stream>>>(
+      msm_finish_team<F><<<(unsigned)((TeamWidth<F>::LANES * batch + 127) / 128), 128, 0, stream>>>(
           batch, sh.groups_per_msm, sh.c, group_out.as<XYZZ<F>>(), out_bytes.as<uint8_t>(), out_inf.as<int>(), M,
           out_xyzz.as<XYZZ<F>>(), opt_finish_affine);
     else
@@ -1268,9 +1268,9 @@ struct Ctx final : kzg_gpu_ctx {
         gen2.x.a.v[i] = C::g2xa(i); gen2.x.b.v[i] = C::g2xb(i);
         gen2.y.a.v[i] = C::g2ya(i); gen2.y.b.v[i] = C::g2yb(i);
       }
-      fixed_base_rows<C, Fp><<<(4 * W + 127) / 128, 128, 0, stream>>>(gen1, t1);
+      fixed_base_rows<C, Fp><<<(TeamWidth<Fp>::LANES * W + 127) / 128, 128, 0, stream>>>(gen1, t1);
       LAUNCHED();
-      fixed_base_rows<C, Fp2><<<(4 * W + 127) / 128, 128, 0, stream>>>(gen2, t2);
+      fixed_base_rows<C, Fp2><<<(TeamWidth<Fp2>::LANES * W + 127) / 128, 128, 0, stream>>>(gen2, t2);
       LAUNCHED();
       for (int level = 0; level + 1 < FB_C; level++) {
         const unsigned grid = (unsigned)(((uint64_t)W << level) + 127) / 128;

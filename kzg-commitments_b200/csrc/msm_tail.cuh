@@ -41,6 +41,7 @@ constexpr int TAIL_SMEM_BYTES = 120 << 10; // dynamic shared memory requested on
 
 // Item distribution: virtual warp v = warp-in-CTA * gridDim + CTA, so consecutive groups of items land on
 // different SMs first and on a second warp of the same SM only after every SM has one.
+template <class F>
 struct TailLane {
   uint64_t vwarp, nvwarps;
   int lane;
@@ -49,12 +50,18 @@ struct TailLane {
     vwarp = (uint64_t)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     nvwarps = (uint64_t)(blockDim.x >> 5) * gridDim.x;
   }
-  __device__ __forceinline__ uint64_t team() const { return vwarp * 8 + (lane >> 2); }
-  __device__ __forceinline__ uint64_t nteams() const { return nvwarps * 8; }
+  template <int LANES> __device__ __forceinline__ uint64_t team() const { return vwarp * (32 / LANES) + (lane / LANES); }
+  template <int LANES> __device__ __forceinline__ uint64_t nteams() const { return nvwarps * (32 / LANES); }
   __device__ __forceinline__ uint64_t thread() const { return vwarp * 32 + lane; }
   __device__ __forceinline__ uint64_t nthreads() const { return nvwarps * 32; }
-  // a level of `items` group operations runs on teams while that takes at most two rounds
-  __device__ __forceinline__ bool use_teams(uint64_t items) const { return items <= 2 * nteams(); }
+  // How a level of `items` group operations runs: on 16-lane teams (G2 only: ~8 us per round, 1184 per round), on
+  // 4-lane teams (G1 6.7 us / G2 ~18 us per round, 4736 per round) while that beats ONE round of one operation per
+  // thread (G1 14.8 us / G2 ~45 us, 18944 per round), else one operation per thread (returns 0).
+  __device__ __forceinline__ int mode(uint64_t items) const {
+    if (TeamWidth<F>::LANES == 16 && items <= 2 * nteams<16>()) return 16;
+    if (items <= 2 * nteams<4>()) return 4;
+    return 0;
+  }
 };
 
 enum TailStage : int {
@@ -88,19 +95,29 @@ struct TailArgs {
   XYZZ<F>* out_xyzz;
 };
 
+// ---- the steps on teams of LANES lanes ---------------------------------------------------------------------
 // one level of two pairwise trees side by side: out[i] = in[2i] + in[2i+1]
+template <class F, int LANES>
+__device__ __forceinline__ void tail_pair_level_teams(const TailLane<F>& tl, const XYZZ<F>* in0, XYZZ<F>* out0, uint64_t n0,
+                                                      const XYZZ<F>* in1, XYZZ<F>* out1, uint64_t n1) {
+  const bool lead = Team<F, LANES>().lead();
+  for (uint64_t t = tl.template team<LANES>(); t < n0 + n1; t += tl.template nteams<LANES>()) {
+    const bool second = t >= n0;
+    const uint64_t i = second ? t - n0 : t;
+    const XYZZ<F>* in = second ? in1 : in0;
+    const XYZZ<F> a = in[2 * i], b = in[2 * i + 1];
+    const XYZZ<F> s = team_add<F, LANES>(a, b);
+    if (lead) (second ? out1 : out0)[i] = s;
+  }
+}
 template <class F>
-__device__ __forceinline__ void tail_pair_level(const TailLane& tl, const XYZZ<F>* in0, XYZZ<F>* out0, uint64_t n0,
+__device__ __forceinline__ void tail_pair_level(const TailLane<F>& tl, const XYZZ<F>* in0, XYZZ<F>* out0, uint64_t n0,
                                                 const XYZZ<F>* in1, XYZZ<F>* out1, uint64_t n1) {
-  if (tl.use_teams(n0 + n1)) {
-    for (uint64_t t = tl.team(); t < n0 + n1; t += tl.nteams()) {
-      const bool second = t >= n0;
-      const uint64_t i = second ? t - n0 : t;
-      const XYZZ<F>* in = second ? in1 : in0;
-      const XYZZ<F> a = in[2 * i], b = in[2 * i + 1];
-      const XYZZ<F> s = team_add<F>(a, b);
-      if ((threadIdx.x & 3) == 0) (second ? out1 : out0)[i] = s;
-    }
+  const int mode = tl.mode(n0 + n1);
+  if (mode == 4) {
+    tail_pair_level_teams<F, 4>(tl, in0, out0, n0, in1, out1, n1);
+  } else if (mode == 16) {
+    if constexpr (TeamWidth<F>::LANES == 16) tail_pair_level_teams<F, 16>(tl, in0, out0, n0, in1, out1, n1);
   } else {
     for (uint64_t t = tl.thread(); t < n0 + n1; t += tl.nthreads()) {
       const bool second = t >= n0;
@@ -115,7 +132,7 @@ __device__ __forceinline__ void tail_pair_level(const TailLane& tl, const XYZZ<F
 
 // halve both trees until one value per sum is left; a grid barrier after every level
 template <class F>
-__device__ __forceinline__ void tail_trees(const TailLane& tl, GridBarrier* bar, XYZZ<F>*& in0, XYZZ<F>*& out0, uint64_t sums0,
+__device__ __forceinline__ void tail_trees(const TailLane<F>& tl, GridBarrier* bar, XYZZ<F>*& in0, XYZZ<F>*& out0, uint64_t sums0,
                                            uint64_t& len0, XYZZ<F>*& in1, XYZZ<F>*& out1, uint64_t sums1, uint64_t& len1) {
   while (len0 > 1 || len1 > 1) {
     tail_pair_level<F>(tl, in0, out0, len0 > 1 ? sums0 * (len0 / 2) : 0, in1, out1, len1 > 1 ? sums1 * (len1 / 2) : 0);
@@ -125,73 +142,143 @@ __device__ __forceinline__ void tail_trees(const TailLane& tl, GridBarrier* bar,
   }
 }
 
+// One level of the segmented fold over the task partials (msm_fold_level_team): a warp scans 32 consecutive slots at a
+// time (coalesced) and its teams then take the few that have work, one per team at a time.
+template <class F, int LANES>
+__device__ __forceinline__ void tail_fold_level(const TailLane<F>& tl, const TailArgs<F>& a, uint32_t stride, uint32_t ntasks) {
+  const Team<F, LANES> tm;
+  constexpr int PER_WARP = 32 / LANES;
+  for (uint64_t q0 = tl.vwarp * 32; q0 < ntasks; q0 += tl.nvwarps * 32) {
+    const uint64_t q = q0 + tl.lane;
+    bool work = false;
+    if (q < ntasks) {
+      const MsmSlotSeg sg = a.slot_seg[q];
+      work = (sg.k & (2u * stride - 1u)) == 0u && sg.k + stride < sg.nt;
+    }
+    unsigned pending = __ballot_sync(0xffffffffu, work);
+    while (pending) {
+      const int my = tl.lane / LANES;
+      unsigned m = pending;
+      int pick = -1;
+      for (int k = 0; k <= my && m; k++) {  // the (my+1)-th set bit
+        pick = __ffs(m) - 1;
+        m &= m - 1;
+        if (k < my) pick = -1;
+      }
+      if (pick >= 0) {
+        const uint64_t qq = q0 + pick;
+        const XYZZ<F> x = a.partial[qq], y = a.partial[qq + stride];
+        const XYZZ<F> s = team_add<F, LANES>(x, y);
+        __syncwarp(tm.mask);  // every lane has read partial[qq] before the leader overwrites it
+        if (tm.lead()) a.partial[qq] = s;
+      }
+      for (int k = 0; k < PER_WARP && pending; k++) pending &= pending - 1;  // drop the ones that were taken
+    }
+  }
+}
+
+// level 0 of the row and column trees, reading bucket values through task_first (msm_bucket_pairs)
+template <class F, int LANES>
+__device__ __forceinline__ void tail_bucket_pairs_teams(const TailLane<F>& tl, const TailArgs<F>& a, const BucketJob<F>& jr,
+                                                        const BucketJob<F>& jc) {
+  const bool lead = Team<F, LANES>().lead();
+  const uint64_t total = jr.total + jc.total;
+  for (uint64_t t0 = tl.template team<LANES>(); t0 < total; t0 += tl.template nteams<LANES>()) {
+    const bool second = t0 >= jr.total;
+    const BucketJob<F>& jb = second ? jc : jr;
+    const uint64_t t = second ? t0 - jr.total : t0;
+    const uint64_t P = jb.len >= 2 ? jb.len / 2 : 1;
+    const uint64_t p = t % P, gs = t / P;
+    const uint64_t s = gs % jb.nsums, g = gs / jb.nsums;
+    const uint64_t b0 = g * a.nb + s * jb.sstride + 2 * p * jb.jstride;
+    XYZZ<F> acc = bucket_value<F>(a.task_first, a.partial, b0);
+    if (jb.len >= 2) acc = team_add<F, LANES>(acc, bucket_value<F>(a.task_first, a.partial, b0 + jb.jstride));
+    if (lead) jb.out[t] = acc;
+  }
+}
+
+// weighted chunks (msm_weighted_chunks): rows and columns side by side
+template <class F, int LANES>
+__device__ __forceinline__ void tail_weighted_teams(const TailLane<F>& tl, const WeightedJob<F>& wr, const WeightedJob<F>& wc) {
+  const bool lead = Team<F, LANES>().lead();
+  const uint64_t total = wr.total + wc.total;
+  for (uint64_t t0 = tl.template team<LANES>(); t0 < total; t0 += tl.template nteams<LANES>()) {
+    const bool second = t0 >= wr.total;
+    const WeightedJob<F>& jb = second ? wc : wr;
+    const uint64_t t = second ? t0 - wr.total : t0;
+    const uint64_t m = jb.m;
+    const uint64_t P = m >= WCHUNK ? m / WCHUNK : 1;
+    const uint64_t p = t % P, g = t / P;
+    const uint64_t j0i = p * WCHUNK, j1i = (j0i + WCHUNK < m) ? j0i + WCHUNK : m;
+    XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
+    for (uint64_t j = j1i; j > j0i; j--) {
+      const XYZZ<F> v = jb.in[g * m + j - 1];
+      run = team_add<F, LANES>(run, v);
+      acc = team_add<F, LANES>(acc, run);
+    }
+    const uint32_t k = (uint32_t)j0i + jb.woff;
+    if (k >= 1) acc = team_add<F, LANES>(acc, team_small_mul<F, LANES>(run, k - 1));
+    else {
+      run.negate();
+      acc = team_add<F, LANES>(acc, run);
+    }
+    if (lead) jb.out[t] = acc;
+  }
+}
+
+// group_out[g] = 2^h * T1[g] + T2[g]
+template <class F, int LANES>
+__device__ __forceinline__ void tail_combine_teams(const TailLane<F>& tl, const TailArgs<F>& a, const XYZZ<F>* rin, const XYZZ<F>* cin) {
+  const bool lead = Team<F, LANES>().lead();
+  for (uint64_t g = tl.template team<LANES>(); g < a.groups; g += tl.template nteams<LANES>()) {
+    XYZZ<F> acc = rin[g];
+    for (int k = 0; k < a.h; k++) acc = team_dbl<F, LANES>(acc);
+    const XYZZ<F> b = cin[g];
+    acc = team_add<F, LANES>(acc, b);
+    if (lead) a.group_out[g] = acc;
+  }
+}
+
+// dispatch on the lane count a level runs with; `thread_mode` is the one-operation-per-thread form
+#define KZG_TAIL_DISPATCH(mode_expr, call4, call16, thread_mode)                \
+  do {                                                                          \
+    const int mode__ = (mode_expr);                                             \
+    if (mode__ == 4) { call4; }                                                 \
+    else if (mode__ == 16) { if constexpr (TeamWidth<F>::LANES == 16) { call16; } } \
+    else { thread_mode; }                                                       \
+  } while (0)
+
 template <class F>
 __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
-  const TailLane tl;
-  const bool lead = (threadIdx.x & 3) == 0;
+  const TailLane<F> tl;
+  constexpr int NARROW = TeamWidth<F>::LANES;  // team width of the steps that are always narrow (finish)
   XYZZ<F>*rin = a.rin, *rout = a.rout, *cin = a.cin, *cout = a.cout;
   uint64_t r_len = a.r_len, c_len = a.c_len;
 
   if (a.first_stage <= TAIL_FOLD && a.last_stage >= TAIL_FOLD) {
-    // Segmented binary tree over the task partials of each bucket (msm_fold_level_team), all levels in one launch.
-    // A warp scans 32 consecutive slots at a time (coalesced) and its teams then take the few that have work.
+    // Segmented binary tree over the task partials of each bucket, all levels in one launch.  At most ntasks / (2 stride)
+    // pairs exist at a level; the fold has no one-operation-per-thread form, so wide levels use the 4-lane teams.
     const uint32_t max_nt = *a.max_nt, ntasks = *a.ntasks_ptr;
     for (uint32_t stride = 1; stride < max_nt; stride <<= 1) {
-      for (uint64_t q0 = tl.vwarp * 32; q0 < ntasks; q0 += tl.nvwarps * 32) {
-        const uint64_t q = q0 + tl.lane;
-        bool work = false;
-        if (q < ntasks) {
-          const MsmSlotSeg sg = a.slot_seg[q];
-          work = (sg.k & (2u * stride - 1u)) == 0u && sg.k + stride < sg.nt;
-        }
-        unsigned pending = __ballot_sync(0xffffffffu, work);
-        while (pending) {  // eight at a time, one per team
-          const int my = tl.lane >> 2;
-          unsigned m = pending;
-          int pick = -1;
-          for (int k = 0; k <= my && m; k++) {  // the (my+1)-th set bit
-            pick = __ffs(m) - 1;
-            m &= m - 1;
-            if (k < my) pick = -1;
-          }
-          if (pick >= 0) {
-            const uint64_t qq = q0 + pick;
-            const XYZZ<F> x = a.partial[qq], y = a.partial[qq + stride];
-            const XYZZ<F> s = team_add<F>(x, y);
-            __syncwarp(Team().mask);  // every lane has read partial[qq] before the leader overwrites it
-            if (lead) a.partial[qq] = s;
-          }
-          for (int k = 0; k < 8 && pending; k++) pending &= pending - 1;  // drop the eight that were taken
-        }
+      const int mode = tl.mode(ntasks / (2 * stride) + 1);
+      if (mode == 16) {
+        if constexpr (TeamWidth<F>::LANES == 16) tail_fold_level<F, 16>(tl, a, stride, ntasks);
+      } else {
+        tail_fold_level<F, 4>(tl, a, stride, ntasks);
       }
       grid_sync(a.barrier);
     }
   }
   if (a.first_stage <= TAIL_BUCKET_PAIRS && a.last_stage >= TAIL_BUCKET_PAIRS) {
-    // level 0 of the row and column trees, reading bucket values through task_first (msm_bucket_pairs)
     const uint64_t Lr = a.Cn >= 2 ? a.Cn / 2 : 1, Lc = a.R >= 2 ? a.R / 2 : 1;
     const BucketJob<F> jr{rin, a.R, a.Cn, a.Cn, 1, a.groups * a.R * Lr};
     const BucketJob<F> jc{cin, a.Cn, a.R, 1, a.Cn, a.groups * a.Cn * Lc};
     const uint64_t total = jr.total + jc.total;
-    if (tl.use_teams(total)) {
-      for (uint64_t t0 = tl.team(); t0 < total; t0 += tl.nteams()) {
-        const bool second = t0 >= jr.total;
-        const BucketJob<F>& jb = second ? jc : jr;
-        const uint64_t t = second ? t0 - jr.total : t0;
-        const uint64_t P = jb.len >= 2 ? jb.len / 2 : 1;
-        const uint64_t p = t % P, gs = t / P;
-        const uint64_t s = gs % jb.nsums, g = gs / jb.nsums;
-        const uint64_t b0 = g * a.nb + s * jb.sstride + 2 * p * jb.jstride;
-        XYZZ<F> acc = bucket_value<F>(a.task_first, a.partial, b0);
-        if (jb.len >= 2) acc = team_add<F>(acc, bucket_value<F>(a.task_first, a.partial, b0 + jb.jstride));
-        if (lead) jb.out[t] = acc;
-      }
-    } else {
-      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
-        const bool second = t0 >= jr.total;
-        msm_bucket_pair_thread<F>(second ? jc : jr, a.nb, a.task_first, a.partial, second ? t0 - jr.total : t0);
-      }
-    }
+    KZG_TAIL_DISPATCH(tl.mode(total), (tail_bucket_pairs_teams<F, 4>(tl, a, jr, jc)), (tail_bucket_pairs_teams<F, 16>(tl, a, jr, jc)),
+                      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+                        const bool second = t0 >= jr.total;
+                        msm_bucket_pair_thread<F>(second ? jc : jr, a.nb, a.task_first, a.partial, second ? t0 - jr.total : t0);
+                      });
     r_len = Lr;
     c_len = Lc;
     grid_sync(a.barrier);
@@ -199,40 +286,16 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
   if (a.first_stage <= TAIL_TREES1 && a.last_stage >= TAIL_TREES1)
     tail_trees<F>(tl, a.barrier, rin, rout, a.groups * a.R, r_len, cin, cout, a.groups * a.Cn, c_len);
   if (a.first_stage <= TAIL_WEIGHTED && a.last_stage >= TAIL_WEIGHTED) {
-    // rin = row sums [groups * R], cin = column sums [groups * Cn]: weighted chunks (msm_weighted_chunks)
+    // rin = row sums [groups * R], cin = column sums [groups * Cn]
     const uint64_t Pr = a.R >= WCHUNK ? a.R / WCHUNK : 1, Pc = a.Cn >= WCHUNK ? a.Cn / WCHUNK : 1;
     const WeightedJob<F> wr{rin, rout, a.R, a.groups * Pr, 0u};
     const WeightedJob<F> wc{cin, cout, a.Cn, a.groups * Pc, 1u};
     const uint64_t total = wr.total + wc.total;
-    if (tl.use_teams(total)) {
-      for (uint64_t t0 = tl.team(); t0 < total; t0 += tl.nteams()) {
-        const bool second = t0 >= wr.total;
-        const WeightedJob<F>& jb = second ? wc : wr;
-        const uint64_t t = second ? t0 - wr.total : t0;
-        const uint64_t m = jb.m;
-        const uint64_t P = m >= WCHUNK ? m / WCHUNK : 1;
-        const uint64_t p = t % P, g = t / P;
-        const uint64_t j0i = p * WCHUNK, j1i = (j0i + WCHUNK < m) ? j0i + WCHUNK : m;
-        XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
-        for (uint64_t j = j1i; j > j0i; j--) {
-          const XYZZ<F> v = jb.in[g * m + j - 1];
-          run = team_add<F>(run, v);
-          acc = team_add<F>(acc, run);
-        }
-        const uint32_t k = (uint32_t)j0i + jb.woff;
-        if (k >= 1) acc = team_add<F>(acc, team_small_mul<F>(run, k - 1));
-        else {
-          run.negate();
-          acc = team_add<F>(acc, run);
-        }
-        if (lead) jb.out[t] = acc;
-      }
-    } else {
-      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
-        const bool second = t0 >= wr.total;
-        msm_weighted_chunk_thread<F>(second ? wc : wr, second ? t0 - wr.total : t0);
-      }
-    }
+    KZG_TAIL_DISPATCH(tl.mode(total), (tail_weighted_teams<F, 4>(tl, wr, wc)), (tail_weighted_teams<F, 16>(tl, wr, wc)),
+                      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+                        const bool second = t0 >= wr.total;
+                        msm_weighted_chunk_thread<F>(second ? wc : wr, second ? t0 - wr.total : t0);
+                      });
     { XYZZ<F>* t = rin; rin = rout; rout = t; }
     { XYZZ<F>* t = cin; cin = cout; cout = t; }
     r_len = Pr;
@@ -242,30 +305,22 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
   if (a.first_stage <= TAIL_TREES2 && a.last_stage >= TAIL_TREES2)
     tail_trees<F>(tl, a.barrier, rin, rout, a.groups, r_len, cin, cout, a.groups, c_len);
   if (a.first_stage <= TAIL_COMBINE && a.last_stage >= TAIL_COMBINE) {
-    // group_out[g] = 2^h * T1[g] + T2[g]
-    if (tl.use_teams(a.groups)) {
-      for (uint64_t g = tl.team(); g < a.groups; g += tl.nteams()) {
-        XYZZ<F> acc = rin[g];
-        for (int k = 0; k < a.h; k++) acc = team_dbl<F>(acc);
-        const XYZZ<F> b = cin[g];
-        acc = team_add<F>(acc, b);
-        if (lead) a.group_out[g] = acc;
-      }
-    } else {
-      for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads()) msm_group_combine_thread<F>(a.h, rin, cin, a.group_out, g);
-    }
+    KZG_TAIL_DISPATCH(tl.mode(a.groups), (tail_combine_teams<F, 4>(tl, a, rin, cin)), (tail_combine_teams<F, 16>(tl, a, rin, cin)),
+                      for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads())
+                        msm_group_combine_thread<F>(a.h, rin, cin, a.group_out, g););
     if (a.last_stage >= TAIL_FINISH) grid_sync(a.barrier);
   }
   if (a.first_stage <= TAIL_FINISH && a.last_stage >= TAIL_FINISH) {
     // one MSM per WARP (its first team): the inversion behind to_affine is a data-dependent loop, and different
     // inversions in one warp would serialise
-    if (tl.lane < 4) {
+    if (tl.lane < NARROW) {
+      const bool lead = tl.lane == 0;
       for (uint64_t m = tl.vwarp; m < a.batch; m += tl.nvwarps) {
         XYZZ<F> acc = a.group_out[m * a.groups_per_msm + (a.groups_per_msm - 1)];
         for (int g = a.groups_per_msm - 2; g >= 0; g--) {
-          for (int k = 0; k < a.c; k++) acc = team_dbl<F>(acc);
+          for (int k = 0; k < a.c; k++) acc = team_dbl<F, NARROW>(acc);
           const XYZZ<F> v = a.group_out[m * a.groups_per_msm + g];
-          acc = team_add<F>(acc, v);
+          acc = team_add<F, NARROW>(acc, v);
         }
         if (lead) {
           if (a.out_xyzz) a.out_xyzz[m] = acc;

@@ -196,7 +196,8 @@ __device__ __forceinline__ void oct_load2(const MixedArray<F>& in, uint64_t i, u
 struct OctLane {
   uint64_t oct, nocts;
   bool lead;
-  __device__ __forceinline__ OctLane(const TailLane& tl) {
+  template <class F>
+  __device__ __forceinline__ OctLane(const TailLane<F>& tl) {
     oct = tl.vwarp * 4 + (tl.lane >> 3);
     nocts = tl.nvwarps * 4;
     lead = (tl.lane & 7) == 0;
@@ -207,7 +208,7 @@ struct OctLane {
 
 // one level of the two pairwise trees; switches an array to projective the first time its level fits the teams
 template <class F>
-__device__ __forceinline__ void tailp_pair_level(const TailLane& tl, const OctLane& ol, MixedArray<F>& in0, MixedArray<F>& out0,
+__device__ __forceinline__ void tailp_pair_level(const TailLane<F>& tl, const OctLane& ol, MixedArray<F>& in0, MixedArray<F>& out0,
                                                  uint64_t n0, MixedArray<F>& in1, MixedArray<F>& out1, uint64_t n1, B3 b3) {
   const bool octs = ol.fits(n0 + n1) || (n0 && !in0.xyzz) || (n1 && !in1.xyzz);
   if (octs) {
@@ -236,7 +237,7 @@ __device__ __forceinline__ void tailp_pair_level(const TailLane& tl, const OctLa
 }
 
 template <class F>
-__device__ __forceinline__ void tailp_trees(const TailLane& tl, const OctLane& ol, GridBarrier* bar, MixedArray<F>& in0,
+__device__ __forceinline__ void tailp_trees(const TailLane<F>& tl, const OctLane& ol, GridBarrier* bar, MixedArray<F>& in0,
                                             MixedArray<F>& out0, uint64_t sums0, uint64_t& len0, MixedArray<F>& in1,
                                             MixedArray<F>& out1, uint64_t sums1, uint64_t& len1, B3 b3) {
   while (len0 > 1 || len1 > 1) {
@@ -249,9 +250,8 @@ __device__ __forceinline__ void tailp_trees(const TailLane& tl, const OctLane& o
 
 template <class F>
 __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, B3 b3) {
-  const TailLane tl;
+  const TailLane<F> tl;
   const OctLane ol(tl);
-  const bool lead4 = (threadIdx.x & 3) == 0;
   // arrays produced before this launch (wide kernels) hold XYZZ values
   MixedArray<F> rin{a.rin, true}, rout{a.rout, true}, cin{a.cin, true}, cout{a.cout, true};
   bool group_xyzz = true;
@@ -261,33 +261,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, 
     // in place on the XYZZ task partials (the wide kernels read them too): 4-lane XYZZ teams as in msm_tail
     const uint32_t max_nt = *a.max_nt, ntasks = *a.ntasks_ptr;
     for (uint32_t stride = 1; stride < max_nt; stride <<= 1) {
-      for (uint64_t q0 = tl.vwarp * 32; q0 < ntasks; q0 += tl.nvwarps * 32) {
-        const uint64_t q = q0 + tl.lane;
-        bool work = false;
-        if (q < ntasks) {
-          const MsmSlotSeg sg = a.slot_seg[q];
-          work = (sg.k & (2u * stride - 1u)) == 0u && sg.k + stride < sg.nt;
-        }
-        unsigned pending = __ballot_sync(0xffffffffu, work);
-        while (pending) {
-          const int my = tl.lane >> 2;
-          unsigned m = pending;
-          int pick = -1;
-          for (int k = 0; k <= my && m; k++) {
-            pick = __ffs(m) - 1;
-            m &= m - 1;
-            if (k < my) pick = -1;
-          }
-          if (pick >= 0) {
-            const uint64_t qq = q0 + pick;
-            const XYZZ<F> x = a.partial[qq], y = a.partial[qq + stride];
-            const XYZZ<F> s = team_add<F>(x, y);
-            __syncwarp(Team().mask);
-            if (lead4) a.partial[qq] = s;
-          }
-          for (int k = 0; k < 8 && pending; k++) pending &= pending - 1;
-        }
-      }
+      tail_fold_level<F, 4>(tl, a, stride, ntasks);
       grid_sync(a.barrier);
     }
   }

@@ -62,11 +62,11 @@ __global__ void setup_powers_kernel(uint64_t n, uint64_t first_index, const uint
 template <class C, class F>
 __global__ void fixed_base_rows(Affine<F> gen, Affine<F>* __restrict__ table) {
   constexpr int W = fb_windows<C>();
-  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 2;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> TeamWidth<F>::SHIFT;
   if (w >= W) return;  // whole teams leave together
   XYZZ<F> acc = XYZZ<F>::from_affine(gen);
   for (int i = 0; i < w * FB_C; i++) acc = team_dbl<F>(acc);
-  if ((threadIdx.x & 3) == 0) table[(size_t)w * FB_HALF] = acc.to_affine();
+  if (Team<F>().lead()) table[(size_t)w * FB_HALF] = acc.to_affine();
 }
 template <class C, class F>
 __global__ void __launch_bounds__(128) fixed_base_fill(int level, Affine<F>* __restrict__ table) {
@@ -161,9 +161,9 @@ template <class F, int MAXW>
 __global__ void __launch_bounds__(128)
 msm_precompute_table_team(uint64_t n, uint64_t stride, int c, int W, const Affine<F>* __restrict__ base,
                           Affine<F>* __restrict__ table_ptr, size_t point_stride) {
-  const uint64_t i = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 2;
+  const uint64_t i = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> TeamWidth<F>::SHIFT;
   if (i >= n) return;  // whole teams leave together
-  const bool lead = (threadIdx.x & 3) == 0;
+  const bool lead = Team<F>().lead();
   struct Strided {
     char* p; size_t st;
     __device__ Affine<F>& operator[](uint64_t k) const { return *reinterpret_cast<Affine<F>*>(p + k * st); }
