@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -960,7 +961,9 @@ struct Ctx final : kzg_gpu_ctx {
   // quotient of poly0 by the k consecutive roots -> qbytes (device, (n-k)*SB bytes)
   // quotients of `batch` polynomials (poly0, stride n) by k consecutive roots each -> qbytes (batch * (n-k) records).
   // d_roots: device array of the first roots (batched form) or nullptr (single polynomial, first_root).
-  int enqueue_quotient(uint64_t n, int64_t first_root, uint64_t k, uint64_t batch = 1, const long long* d_roots = nullptr) {
+  // h_roots: the same first roots on the host (lets a batch opened at few distinct positions share Z and 1 / rev(Z)).
+  int enqueue_quotient(uint64_t n, int64_t first_root, uint64_t k, uint64_t batch = 1, const long long* d_roots = nullptr,
+                       const int64_t* h_roots = nullptr) {
     const Fr* q;
     // measured on B200 at degree 4095 (tools/gpu_probe_quotient.py): the scan kernel costs 0.08 ms per root, the
     // power-series path 0.69 ms whatever k is -> series from 8 roots on
@@ -976,6 +979,46 @@ struct Ctx final : kzg_gpu_ctx {
                                    ? 300.0 + (double)Lq * (double)Lq / 42e3 : 1e300;
     const bool series = cost_series < cost_cta && cost_series < cost_grid;
     const bool rounds_grid = !series && cost_grid < cost_cta && opt_long_division >= 3;
+    // A batch with many roots: the systolic kernel runs one CTA per polynomial at ~184 M products/s (k L products each,
+    // ~2 CTAs per SM), whatever the batch size.  When the polynomials are opened at few distinct positions — the usual
+    // case: every blob at the same points — Z and the inverse series of rev(Z) are computed once per position over the
+    // whole GPU and each polynomial only needs the last truncated product (L^2 / 2 products at the rate of the whole
+    // GPU, ~268 products/ns): cheaper for every batch size, and it fills the machine for small batches.
+    std::vector<long long> positions;
+    bool batch_series = false;
+    if (!single && d_roots && h_roots && opt_long_division >= 3 && k >= 48 && k <= 65536 && Lq <= 65536) {
+      positions.assign(h_roots, h_roots + batch);
+      std::sort(positions.begin(), positions.end());
+      positions.erase(std::unique(positions.begin(), positions.end()), positions.end());
+      const double cost_shared = (double)positions.size() * (310.0 + (double)Lq * (double)Lq / 42e3) +
+                                 (double)batch * (double)Lq * (double)Lq / 268e3;
+      const double cost_systolic = std::ceil((double)batch / 296.0) * ((double)k * (double)Lq / 184.0);
+      batch_series = positions.size() <= 64 && cost_shared < cost_systolic;
+    }
+    // g = rev(Z)^-1 mod x^L for the k consecutive roots from `root` on (Newton doubling over truncated products)
+    auto grid_for = [](uint64_t outs) { return (unsigned)std::min<uint64_t>((outs + 3) / 4, 148 * 32); };
+    auto inverse_series = [&](int64_t root, Fr** g_out) -> int {
+      Fr *pz = nullptr, *zz = nullptr;
+      int rc = enqueue_interpolate(root, k, &pz, &zz, false);  // Z (k + 1 coefficients, monic)
+      if (rc) return rc;
+      const uint64_t L = n - k;
+      for (DevBuf* bf : {&nt_g0, &nt_g1, &nt_u}) CK(bf->ensure(L * sizeof(Fr)));
+      Fr *g = nt_g0.as<Fr>(), *g2 = nt_g1.as<Fr>(), *u = nt_u.as<Fr>();
+      // g = 1 / rev(Z) mod x^1 = 1 (Z is monic); f = rev(Z) is read in place: f[t] = Z[k - t], only its first
+      // min(k + 1, 2m) coefficients matter at precision 2m
+      poly_mul_trunc<C><<<1, 128, 0, stream>>>(zz, 1, (long long)k, zz, 1, (long long)k, g, 1, 0, 0);  // 1 * 1
+      LAUNCHED();
+      for (uint64_t m = 1; m < L; m <<= 1) {
+        const uint64_t m2 = std::min<uint64_t>(2 * m, L), nf = std::min<uint64_t>(k + 1, m2);
+        poly_mul_trunc<C><<<grid_for(m2), 128, 0, stream>>>(zz, nf, (long long)k, g, m, -1, u, m2, 1, 0);   // u = 2 - f g
+        LAUNCHED();
+        poly_mul_trunc<C><<<grid_for(m2), 128, 0, stream>>>(g, m, -1, u, m2, -1, g2, m2, 0, 0);              // g' = g u
+        LAUNCHED();
+        std::swap(g, g2);
+      }
+      *g_out = g;
+      return KZG_GPU_OK;
+    };
     if (rounds_grid) {
       int rcb = ensure_barrier();
       if (rcb) return rcb;
@@ -999,28 +1042,29 @@ struct Ctx final : kzg_gpu_ctx {
       q = (k & 1) ? poly1.as<Fr>() : poly0.as<Fr>();
     } else if (series) {
       // one polynomial, many roots: rev(q) = rev(P) * rev(Z)^-1 mod x^L, all truncated products over the whole GPU
-      Fr *pz = nullptr, *zz = nullptr;
-      int rc = enqueue_interpolate(first_root, k, &pz, &zz, false);  // Z (k + 1 coefficients, monic)
+      Fr* g = nullptr;
+      int rc = inverse_series(first_root, &g);
       if (rc) return rc;
       const uint64_t L = n - k;
-      for (DevBuf* bf : {&nt_g0, &nt_g1, &nt_u}) CK(bf->ensure(L * sizeof(Fr)));
-      Fr *g = nt_g0.as<Fr>(), *g2 = nt_g1.as<Fr>(), *u = nt_u.as<Fr>();
-      auto grid_for = [](uint64_t outs) { return (unsigned)std::min<uint64_t>((outs + 3) / 4, 148 * 32); };
-      // g = 1 / rev(Z) mod x^1 = 1 (Z is monic); f = rev(Z) is read in place: f[t] = Z[k - t], only its first
-      // min(k + 1, 2m) coefficients matter at precision 2m
-      poly_mul_trunc<C><<<1, 128, 0, stream>>>(zz, 1, (long long)k, zz, 1, (long long)k, g, 1, 0, 0);  // 1 * 1
-      LAUNCHED();
-      for (uint64_t m = 1; m < L; m <<= 1) {
-        const uint64_t m2 = std::min<uint64_t>(2 * m, L), nf = std::min<uint64_t>(k + 1, m2);
-        poly_mul_trunc<C><<<grid_for(m2), 128, 0, stream>>>(zz, nf, (long long)k, g, m, -1, u, m2, 1, 0);   // u = 2 - f g
-        LAUNCHED();
-        poly_mul_trunc<C><<<grid_for(m2), 128, 0, stream>>>(g, m, -1, u, m2, -1, g2, m2, 0, 0);              // g' = g u
-        LAUNCHED();
-        std::swap(g, g2);
-      }
       // rev(q) = rev(P)[0..L) * g mod x^L, written back to front: q[i] = rev(q)[L - 1 - i]
       poly_mul_trunc<C><<<grid_for(L), 128, 0, stream>>>(poly0.as<Fr>(), L, (long long)(n - 1), g, L, -1, poly1.as<Fr>(), L, 0, 1);
       LAUNCHED();
+      q = poly1.as<Fr>();
+    } else if (batch_series) {
+      const uint64_t L = n - k;
+      const unsigned gx = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((L + 3) / 4, (148 * 32 + batch - 1) / batch));
+      for (long long pos : positions) {
+        Fr* g = nullptr;
+        int rc = inverse_series(pos, &g);
+        if (rc) return rc;
+        for (uint64_t y0 = 0; y0 < batch; y0 += 65535) {  // gridDim.y limit
+          const uint64_t ny = std::min<uint64_t>(65535, batch - y0);
+          poly_mul_trunc<C><<<dim3(gx, (unsigned)ny), 128, 0, stream>>>(
+              poly0.as<Fr>() + y0 * n, L, (long long)(n - 1), g, L, -1, poly1.as<Fr>() + y0 * n, L, 0, 1, n, n,
+              positions.size() > 1 ? d_roots + y0 : nullptr, pos);
+          LAUNCHED();
+        }
+      }
       q = poly1.as<Fr>();
     } else if (batch == 1 && !d_roots && k <= 4096 && opt_long_division) {
       // one polynomial, many roots: Z from the product tree (no P part), then CTA-wide long division
@@ -1145,7 +1189,7 @@ struct Ctx final : kzg_gpu_ctx {
       if (rc) return rc;
       CK(roots.ensure(nb * sizeof(long long)));
       CK(cudaMemcpyAsync(roots.p, first_roots + b0, nb * sizeof(long long), cudaMemcpyHostToDevice, stream));
-      rc = enqueue_quotient(n, 0, k, nb, roots.as<long long>());
+      rc = enqueue_quotient(n, 0, k, nb, roots.as<long long>(), first_roots + b0);
       if (rc) return rc;
       rc = msm(1, qbytes.as<uint8_t>(), true, n - k, nb, 0, out ? out + b0 * (size_t)(2 * M) : nullptr,
                is_inf ? is_inf + b0 : nullptr, true);

@@ -556,12 +556,20 @@ poly_long_division_cluster(uint64_t n, uint32_t k, const Field<typename C::FrP>*
 // out[i] = sum_t a[t] b[i - t] (i < nout);  two_minus: out = 2 [i == 0] - that.  With a_rev / b_rev the operand
 // is read back to front (a[t] := a_base[a_last - t]), which is how rev(P) and rev(Z) are consumed in place, and
 // out_rev writes the result back to front (out[nout - 1 - i]).
+// Batched form (blockIdx.y = polynomial): a and out advance by a_stride / out_stride coefficients per polynomial
+// while b is shared — the last product of the quotient, rev(P_y) * rev(Z)^-1, for every polynomial of a batch that
+// is opened at the same points.  With `sel`, polynomial y takes part only if sel[y] == sel_value.
 template <class C>
 __global__ void __launch_bounds__(128)
 poly_mul_trunc(const Field<typename C::FrP>* __restrict__ a, uint64_t na, long long a_last,
                const Field<typename C::FrP>* __restrict__ b, uint64_t nb, long long b_last,
-               Field<typename C::FrP>* __restrict__ out, uint64_t nout, int two_minus, int out_rev) {
+               Field<typename C::FrP>* __restrict__ out, uint64_t nout, int two_minus, int out_rev,
+               uint64_t a_stride = 0, uint64_t out_stride = 0, const long long* __restrict__ sel = nullptr,
+               long long sel_value = 0) {
   using Fr = Field<typename C::FrP>;
+  if (sel && sel[blockIdx.y] != sel_value) return;
+  a += blockIdx.y * a_stride;
+  out += blockIdx.y * out_stride;
   const int lane = threadIdx.x & 31;
   const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
   const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;

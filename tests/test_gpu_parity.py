@@ -447,6 +447,38 @@ def test_prove_batch_equals_single_proofs(ctxs, cname):
     assert all(infs) and out == bytes(len(out))
 
 
+@pytest.mark.parametrize("cname", ["bls12381", "bn254"])
+def test_prove_batch_many_roots_shared_positions(ctxs, cname):
+    """A batch opened at many points but few distinct positions: Z and 1 / rev(Z) once per position, one batched truncated
+    product for the quotients (ctx.cuh enqueue_quotient, batch_series) — against the systolic kernel (long_division = 0)
+    and against kzg_gpu_prove one polynomial at a time."""
+    C = get_curve(cname)
+    ctx = ctxs(cname)
+    rng = random.Random(77 + C.id)
+    n, batch, k = 700, 6, 400
+    ts = kzg_b200.TrustedSetup.generate(cname, n + 1, rng.randrange(C.r), ctx=ctx)
+    polys = [[rng.randrange(C.r) for _ in range(n)] for _ in range(batch)]
+    polys[2] = [0] * n
+    polys[4] = polys[4][:500] + [0] * 200   # lower degree than the rest
+    raw = b"".join(C.scalars_to_bytes(p) for p in polys)
+    for roots in ([7] * batch, [7, 7, 9, 9, 7, 9], [0, 1, 2, 3, 4, 5]):
+        ctx.set_option("long_division", 3)
+        out, infs = ctx.prove_batch(raw, n, roots, k)
+        ctx.set_option("long_division", 0)
+        out0, infs0 = ctx.prove_batch(raw, n, roots, k)
+        ctx.set_option("long_division", 3)
+        assert out == out0 and infs == infs0, roots
+        for b in range(batch):
+            xy, inf = ctx.prove(C.scalars_to_bytes(polys[b]), roots[b], k)
+            assert out[b * 2 * ctx.M:(b + 1) * 2 * ctx.M] == xy and infs[b] == inf, (roots, b)
+        assert infs[2]
+    # and against the oracle: proof = [q(s)]G1 with q from the CPU restatement of NTL's div
+    out, infs = ctx.prove_batch(raw, n, [7] * batch, k)
+    q, _, _ = C.poly_quotient(polys[1], 7, k)
+    xy, inf = ctx.msm_g1(C.scalars_to_bytes(q), len(q))
+    assert out[2 * ctx.M:4 * ctx.M] == xy and not inf
+
+
 @pytest.mark.parametrize("cname", CURVE_NAMES)
 def test_commit_bytes_device_chain(ctxs, cname):
     """SURVEY 8(f) N2: blob::from_bytes -> poly::from_blob -> create_commit chained on the device
