@@ -74,7 +74,7 @@ void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
  * pre-reduction levels, -1 = auto = off), "finish_affine" (0: an MSM leaves only its projective result for
  * kzg_gpu_msm_partial_device — the point-range split folds and normalises once, after the exchange).
  * "tail" (1: the sort and the narrow end of the reduction run in two persistent cooperative kernels), "tail_proj" (1: that
- * end uses complete projective formulas on 8-lane teams for G1), "table_pad" (experiment: 128-byte window-table entries),
+ * end uses complete projective formulas on 8-lane teams for G1; 2: also for G2, on whole-warp teams), "table_pad" (experiment: 128-byte window-table entries),
  * "barrier_sleep" (ns between polls of the grid barrier).
  * Takes effect at the next srs_load / setup_powers / MSM. */
 int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value);
@@ -176,7 +176,8 @@ int kzg_gpu_msm_stats(kzg_gpu_ctx* ctx, uint64_t* out, int n);
  * kinds 4..7: LATENCY probes in the configuration of the reduction tail (one CTA of 128 threads per SM), returned as
  * steps per second of ONE dependent chain: 4 = grid barriers, 5 = 4-lane team additions (XYZZ, G1 field),
  * 6 = single-thread additions, 7 = dependent Fp Montgomery products, 8 = Fp inversions (batched divsteps),
- * 9 = Fp inversions by the binary extended GCD of round 1 (kept as a cross-check) */
+ * 9 = Fp inversions by the binary extended GCD of round 1 (kept as a cross-check), 10 / 11 = G2 additions on 16-lane /
+ * 4-lane XYZZ teams, 12 = G2 additions on whole-warp projective teams, 13 = G1 additions on 8-lane projective teams */
 int kzg_gpu_microbench(kzg_gpu_ctx* ctx, int kind, double* ops_per_second);
 
 /* Device self-test: field, Fp2 and group-law identities on random inputs, compared on device against

@@ -411,8 +411,7 @@ struct Ctx final : kzg_gpu_ctx {
   int prepare_tail() {
     if (tail_ready[std::is_same<F, Fp2>::value ? 1 : 0]) return ensure_barrier();
     CK(cudaFuncSetAttribute(msm_tail<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
-    if constexpr (std::is_same<F, Fp>::value)
-      CK(cudaFuncSetAttribute(msm_tail_proj<Fp>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(msm_tail_proj<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, TAIL_SMEM_BYTES));
     int rcb = ensure_barrier();
     if (rcb) return rcb;
     tail_ready[std::is_same<F, Fp2>::value ? 1 : 0] = true;
@@ -627,13 +626,17 @@ struct Ctx final : kzg_gpu_ctx {
       ta.rin = rin; ta.rout = rout; ta.cin = cin; ta.cout = cout;
       ta.r_len = r_len; ta.c_len = c_len;
       (void)items;  // always one CTA per SM: narrow levels are dealt out one warp per SM first (msm_tail.cuh)
-      // G1: complete projective formulas on 8-lane teams, two product rounds per addition.  G2 was measured both ways
-      // (profiles/r2k_probe_g2.json: 1.24 vs 1.23 ms at 4097 terms — over Fp2 the replicated linear steps and the
-      // register spills of the 8-lane form eat what the shorter product chain saves), so it keeps the XYZZ teams.
+      // Complete projective formulas, two product rounds per addition: G1 on 8-lane teams ("tail_proj" >= 1), G2 on
+      // whole warps — 8 roles x the 3 Karatsuba parts of an Fp2 product ("tail_proj" = 2; msm_tail_proj.cuh).
       if constexpr (std::is_same<F, Fp>::value) {
         if (opt_tail_proj) {
           B3 b3{3 * C::G1_B, 0};
           return launch_cooperative((const void*)msm_tail_proj<Fp>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES, &b3);
+        }
+      } else {
+        if (opt_tail_proj >= 2) {
+          B3 b3{3 * C::G2_B_RE, 3 * C::G2_B_IM};
+          return launch_cooperative((const void*)msm_tail_proj<Fp2>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES, &b3);
         }
       }
       return launch_cooperative((const void*)msm_tail<F>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES);
@@ -1423,7 +1426,7 @@ struct Ctx final : kzg_gpu_ctx {
   int microbench(int kind, double* ops) override {
     std::lock_guard<std::recursive_mutex> lock(mu);
     CK(cudaSetDevice(device));
-    if (!ops || kind < 0 || kind > 9) return KZG_GPU_ERR_ARG;
+    if (!ops || kind < 0 || kind > 13) return KZG_GPU_ERR_ARG;
     CK(scal.ensure(64));
     if (kind >= 4) return microbench_latency(kind, ops);
     const int blocks = 148 * 8, threads = 256;
@@ -1462,7 +1465,7 @@ struct Ctx final : kzg_gpu_ctx {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    const int iters = kind == 4 ? 2000 : kind == 7 ? 4000 : kind >= 8 ? 50 : 400;
+    const int iters = kind == 4 ? 2000 : kind == 7 ? 4000 : kind >= 10 ? 400 : kind >= 8 ? 50 : 400;
     float best = 1e30f;
     for (int rep = 0; rep < 3; rep++) {
       CK(cudaEventRecord(e0, stream));
@@ -1477,7 +1480,12 @@ struct Ctx final : kzg_gpu_ctx {
         CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)cap), dim3(TAIL_THREADS), params, 0, stream));
         launches++;
       } else {
-        bench_latency_chain<Fp><<<num_sms > 0 ? num_sms : 148, TAIL_THREADS, 0, stream>>>(kind, iters, 777u + rep, scal.as<uint32_t>());
+        if (kind >= 10) {
+          B3 b3{kind == 13 ? 3 * C::G1_B : 3 * C::G2_B_RE, kind == 13 ? 0 : 3 * C::G2_B_IM};
+          bench_latency_chain_g2<Fp, Fp2><<<num_sms > 0 ? num_sms : 148, TAIL_THREADS, 0, stream>>>(kind, iters, 777u + rep, b3, scal.as<uint32_t>());
+        } else {
+          bench_latency_chain<Fp><<<num_sms > 0 ? num_sms : 148, TAIL_THREADS, 0, stream>>>(kind, iters, 777u + rep, scal.as<uint32_t>());
+        }
         LAUNCHED();
       }
       CK(cudaEventRecord(e1, stream));

@@ -248,6 +248,49 @@ __device__ __forceinline__ void tail_combine_teams(const TailLane<F>& tl, const 
     else { thread_mode; }                                                       \
   } while (0)
 
+// ---- the steps on XYZZ values, every level in the form TailLane::mode picks (shared with msm_tail_proj.cuh, which
+// ---- uses them for the levels that are too wide for its projective teams)
+template <class F>
+__device__ __forceinline__ void tail_fold_xyzz(const TailLane<F>& tl, const TailArgs<F>& a) {
+  // Segmented binary tree over the task partials of each bucket, all levels in one launch.  At most ntasks / (2 stride)
+  // pairs exist at a level; the fold has no one-operation-per-thread form, so wide levels use the 4-lane teams.
+  const uint32_t max_nt = *a.max_nt, ntasks = *a.ntasks_ptr;
+  for (uint32_t stride = 1; stride < max_nt; stride <<= 1) {
+    const int mode = tl.mode(ntasks / (2 * stride) + 1);
+    if (mode == 16) {
+      if constexpr (TeamWidth<F>::LANES == 16) tail_fold_level<F, 16>(tl, a, stride, ntasks);
+    } else {
+      tail_fold_level<F, 4>(tl, a, stride, ntasks);
+    }
+    grid_sync(a.barrier);
+  }
+}
+template <class F>
+__device__ __forceinline__ void tail_bucket_pairs_xyzz(const TailLane<F>& tl, const TailArgs<F>& a, const BucketJob<F>& jr,
+                                                       const BucketJob<F>& jc) {
+  const uint64_t total = jr.total + jc.total;
+  KZG_TAIL_DISPATCH(tl.mode(total), (tail_bucket_pairs_teams<F, 4>(tl, a, jr, jc)), (tail_bucket_pairs_teams<F, 16>(tl, a, jr, jc)),
+                    for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+                      const bool second = t0 >= jr.total;
+                      msm_bucket_pair_thread<F>(second ? jc : jr, a.nb, a.task_first, a.partial, second ? t0 - jr.total : t0);
+                    });
+}
+template <class F>
+__device__ __forceinline__ void tail_weighted_xyzz(const TailLane<F>& tl, const WeightedJob<F>& wr, const WeightedJob<F>& wc) {
+  const uint64_t total = wr.total + wc.total;
+  KZG_TAIL_DISPATCH(tl.mode(total), (tail_weighted_teams<F, 4>(tl, wr, wc)), (tail_weighted_teams<F, 16>(tl, wr, wc)),
+                    for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
+                      const bool second = t0 >= wr.total;
+                      msm_weighted_chunk_thread<F>(second ? wc : wr, second ? t0 - wr.total : t0);
+                    });
+}
+template <class F>
+__device__ __forceinline__ void tail_combine_xyzz(const TailLane<F>& tl, const TailArgs<F>& a, const XYZZ<F>* rin, const XYZZ<F>* cin) {
+  KZG_TAIL_DISPATCH(tl.mode(a.groups), (tail_combine_teams<F, 4>(tl, a, rin, cin)), (tail_combine_teams<F, 16>(tl, a, rin, cin)),
+                    for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads())
+                      msm_group_combine_thread<F>(a.h, rin, cin, a.group_out, g););
+}
+
 template <class F>
 __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
   const TailLane<F> tl;
@@ -255,30 +298,12 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
   XYZZ<F>*rin = a.rin, *rout = a.rout, *cin = a.cin, *cout = a.cout;
   uint64_t r_len = a.r_len, c_len = a.c_len;
 
-  if (a.first_stage <= TAIL_FOLD && a.last_stage >= TAIL_FOLD) {
-    // Segmented binary tree over the task partials of each bucket, all levels in one launch.  At most ntasks / (2 stride)
-    // pairs exist at a level; the fold has no one-operation-per-thread form, so wide levels use the 4-lane teams.
-    const uint32_t max_nt = *a.max_nt, ntasks = *a.ntasks_ptr;
-    for (uint32_t stride = 1; stride < max_nt; stride <<= 1) {
-      const int mode = tl.mode(ntasks / (2 * stride) + 1);
-      if (mode == 16) {
-        if constexpr (TeamWidth<F>::LANES == 16) tail_fold_level<F, 16>(tl, a, stride, ntasks);
-      } else {
-        tail_fold_level<F, 4>(tl, a, stride, ntasks);
-      }
-      grid_sync(a.barrier);
-    }
-  }
+  if (a.first_stage <= TAIL_FOLD && a.last_stage >= TAIL_FOLD) tail_fold_xyzz<F>(tl, a);
   if (a.first_stage <= TAIL_BUCKET_PAIRS && a.last_stage >= TAIL_BUCKET_PAIRS) {
     const uint64_t Lr = a.Cn >= 2 ? a.Cn / 2 : 1, Lc = a.R >= 2 ? a.R / 2 : 1;
     const BucketJob<F> jr{rin, a.R, a.Cn, a.Cn, 1, a.groups * a.R * Lr};
     const BucketJob<F> jc{cin, a.Cn, a.R, 1, a.Cn, a.groups * a.Cn * Lc};
-    const uint64_t total = jr.total + jc.total;
-    KZG_TAIL_DISPATCH(tl.mode(total), (tail_bucket_pairs_teams<F, 4>(tl, a, jr, jc)), (tail_bucket_pairs_teams<F, 16>(tl, a, jr, jc)),
-                      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
-                        const bool second = t0 >= jr.total;
-                        msm_bucket_pair_thread<F>(second ? jc : jr, a.nb, a.task_first, a.partial, second ? t0 - jr.total : t0);
-                      });
+    tail_bucket_pairs_xyzz<F>(tl, a, jr, jc);
     r_len = Lr;
     c_len = Lc;
     grid_sync(a.barrier);
@@ -290,12 +315,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
     const uint64_t Pr = a.R >= WCHUNK ? a.R / WCHUNK : 1, Pc = a.Cn >= WCHUNK ? a.Cn / WCHUNK : 1;
     const WeightedJob<F> wr{rin, rout, a.R, a.groups * Pr, 0u};
     const WeightedJob<F> wc{cin, cout, a.Cn, a.groups * Pc, 1u};
-    const uint64_t total = wr.total + wc.total;
-    KZG_TAIL_DISPATCH(tl.mode(total), (tail_weighted_teams<F, 4>(tl, wr, wc)), (tail_weighted_teams<F, 16>(tl, wr, wc)),
-                      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
-                        const bool second = t0 >= wr.total;
-                        msm_weighted_chunk_thread<F>(second ? wc : wr, second ? t0 - wr.total : t0);
-                      });
+    tail_weighted_xyzz<F>(tl, wr, wc);
     { XYZZ<F>* t = rin; rin = rout; rout = t; }
     { XYZZ<F>* t = cin; cin = cout; cout = t; }
     r_len = Pr;
@@ -305,9 +325,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail(TailArgs<F> a) {
   if (a.first_stage <= TAIL_TREES2 && a.last_stage >= TAIL_TREES2)
     tail_trees<F>(tl, a.barrier, rin, rout, a.groups, r_len, cin, cout, a.groups, c_len);
   if (a.first_stage <= TAIL_COMBINE && a.last_stage >= TAIL_COMBINE) {
-    KZG_TAIL_DISPATCH(tl.mode(a.groups), (tail_combine_teams<F, 4>(tl, a, rin, cin)), (tail_combine_teams<F, 16>(tl, a, rin, cin)),
-                      for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads())
-                        msm_group_combine_thread<F>(a.h, rin, cin, a.group_out, g););
+    tail_combine_xyzz<F>(tl, a, rin, cin);
     if (a.last_stage >= TAIL_FINISH) grid_sync(a.barrier);
   }
   if (a.first_stage <= TAIL_FINISH && a.last_stage >= TAIL_FINISH) {

@@ -14,9 +14,10 @@
 // msm_tail_proj is msm_tail (msm_tail.cuh) with these operations for every step that is narrow enough for the
 // 8-lane teams; the fold of the task partials (in place on the XYZZ partials that the wide kernels also read) and
 // levels of more than 4 rounds of teams keep XYZZ, converted on first use (X ZZZ : Y ZZ : ZZ ZZZ, one round).
-// The code is generic over Fp2 as well (the twist constants are tiny too: b' = 5 + 5i, 1 - i, 4 + 4i) and was measured
-// for G2 (profiles/r2k_probe_g2.json): no gain — 255 registers with spills and twice the linear work per step — so
-// ctx.cuh instantiates it for G1 only and G2 keeps msm_tail.
+// G2 (the twist constants are tiny too: b' = 5 + 5i, 1 - i, 4 + 4i): with an Fp2 product done whole by one lane (three
+// dependent Fp products) the 8-lane form brought nothing (profiles/r2k_probe_g2.json).  ProjTeam<Fp2> therefore spreads
+// one operation over the WHOLE WARP: 8 roles x 4 lanes, a role's Fp2 product split into its three Karatsuba Fp
+// products (as the 16-lane XYZZ teams of msm_team.cuh), so a G2 addition is also two Fp products deep.
 #pragma once
 #include "msm_tail.cuh"
 
@@ -29,14 +30,50 @@ struct Proj {
   __device__ __forceinline__ bool is_inf() const { return Z.is_zero(); }
 };
 
-struct Octet {
+// The lanes that share one projective operation.  G1: 8 lanes, one product of the round per lane (roles 0..5 used).
+// G2: the whole warp = 8 roles x 4 parts; part 0 / 1 / 2 compute a a' / b b' / (a + b)(a' + b') of the role's Fp2 product.
+template <class F> struct ProjTeam;
+template <class P>
+struct ProjTeam<Field<P>> {
+  using F = Field<P>;
+  using Piece = F;
+  static constexpr int LANES = 8;
   int role, base;
   unsigned mask;
-  __device__ __forceinline__ Octet() {
+  __device__ __forceinline__ ProjTeam() {
     const int lane = threadIdx.x & 31;
     role = lane & 7;
     base = lane & ~7;
     mask = 0xFFu << base;
+  }
+  __device__ __forceinline__ Piece piece(const F& u, const F& v) const { return F::mul(u, v); }
+  __device__ __forceinline__ F product(const Piece& m, int r) const { return team_shfl(mask, m, base + r); }
+};
+template <class P>
+struct ProjTeam<Field2<P>> {
+  using F = Field2<P>;
+  using Base = Field<P>;
+  using Piece = Base;
+  static constexpr int LANES = 32;
+  int role, part;
+  static constexpr unsigned mask = 0xffffffffu;
+  __device__ __forceinline__ ProjTeam() {
+    const int lane = threadIdx.x & 31;
+    role = lane >> 2;
+    part = lane & 3;
+  }
+  // Karatsuba recombination by the role's own lanes (see team_piece in msm_team.cuh): part 0 ends up with the real,
+  // part 1 with the imaginary component of the role's product
+  __device__ __forceinline__ Piece piece(const F& u, const F& v) const {
+    const Base x = part == 0 ? u.a : part == 1 ? u.b : Base::add(u.a, u.b);
+    const Base y = part == 0 ? v.a : part == 1 ? v.b : Base::add(v.a, v.b);
+    const Base m = Base::mul(x, y);
+    const int lane = threadIdx.x & 31;
+    const Base other = team_shfl(mask, m, lane ^ 1), third = team_shfl(mask, m, (lane & ~3) | 2);
+    return Base::sub(Base::sub(part == 0 ? m : third, other), part == 0 ? Base::zero() : m);
+  }
+  __device__ __forceinline__ F product(const Piece& m, int r) const {
+    return F{team_shfl(mask, m, 4 * r), team_shfl(mask, m, 4 * r + 1)};
   }
 };
 
@@ -77,18 +114,17 @@ __device__ __forceinline__ Field2<P> mul_small(const Field2<P>& x, B3 k) {
 // a + b, complete (RCB Algorithm 7 with a = 0, b3 = 3b).  a, b and the result are replicated on the 8 lanes.
 template <class F>
 __device__ __noinline__ Proj<F> oct_add(const Proj<F>& a, const Proj<F>& b, B3 b3) {
-  const Octet tm;
-  const int r = tm.role, base = tm.base;
-  const unsigned mask = tm.mask;
+  const ProjTeam<F> tm;
+  const int r = tm.role;
   // round 1:  X1X2 | Y1Y2 | Z1Z2 | (X1+Y1)(X2+Y2) | (Y1+Z1)(Y2+Z2) | (X1+Z1)(X2+Z2)
   F u = r == 0 ? a.X : r == 1 ? a.Y : a.Z, v = r == 0 ? b.X : r == 1 ? b.Y : b.Z;
   if (r >= 3) {  // (uniform inside a team only per lane: both sides are cheap, the compiler predicates them)
     u = F::add(r == 4 ? a.Y : a.X, r == 3 ? a.Y : a.Z);
     v = F::add(r == 4 ? b.Y : b.X, r == 3 ? b.Y : b.Z);
   }
-  const F m1 = F::mul(u, v);
-  const F t0 = team_shfl(mask, m1, base), t1o = team_shfl(mask, m1, base + 1), t2o = team_shfl(mask, m1, base + 2);
-  F t3 = team_shfl(mask, m1, base + 3), t4 = team_shfl(mask, m1, base + 4), y3 = team_shfl(mask, m1, base + 5);
+  const auto m1 = tm.piece(u, v);
+  const F t0 = tm.product(m1, 0), t1o = tm.product(m1, 1), t2o = tm.product(m1, 2);
+  F t3 = tm.product(m1, 3), t4 = tm.product(m1, 4), y3 = tm.product(m1, 5);
   t3 = F::sub(F::sub(t3, t0), t1o);                // X1Y2 + X2Y1
   t4 = F::sub(F::sub(t4, t1o), t2o);               // Y1Z2 + Y2Z1
   y3 = mul_small(F::sub(F::sub(y3, t0), t2o), b3); // b3 (X1Z2 + X2Z1)
@@ -98,48 +134,46 @@ __device__ __noinline__ Proj<F> oct_add(const Proj<F>& a, const Proj<F>& b, B3 b
   // round 2:  t4 y3 | t3 t1 | y3 x3 | t1 z3 | x3 t3 | z3 t4
   const F p = r == 0 ? t4 : r == 1 ? t3 : r == 2 ? y3 : r == 3 ? t1 : r == 4 ? x3 : z3;
   const F q = r == 0 ? y3 : r == 1 ? t1 : r == 2 ? x3 : r == 3 ? z3 : r == 4 ? t3 : t4;
-  const F m2 = F::mul(p, q);
+  const auto m2 = tm.piece(p, q);
   Proj<F> o;
-  o.X = F::sub(team_shfl(mask, m2, base + 1), team_shfl(mask, m2, base));
-  o.Y = F::add(team_shfl(mask, m2, base + 3), team_shfl(mask, m2, base + 2));
-  o.Z = F::add(team_shfl(mask, m2, base + 5), team_shfl(mask, m2, base + 4));
+  o.X = F::sub(tm.product(m2, 1), tm.product(m2, 0));
+  o.Y = F::add(tm.product(m2, 3), tm.product(m2, 2));
+  o.Z = F::add(tm.product(m2, 5), tm.product(m2, 4));
   return o;
 }
 
 // 2 a, complete (RCB Algorithm 9 with a = 0)
 template <class F>
 __device__ __noinline__ Proj<F> oct_dbl(const Proj<F>& a, B3 b3) {
-  const Octet tm;
-  const int r = tm.role, base = tm.base;
-  const unsigned mask = tm.mask;
+  const ProjTeam<F> tm;
+  const int r = tm.role;
   // round 1:  Y Y | Y Z | Z Z | X Y
-  const F m1 = F::mul(r == 2 ? a.Z : r >= 3 ? a.X : a.Y, r == 0 || r >= 3 ? a.Y : a.Z);
-  const F t0 = team_shfl(mask, m1, base), t1 = team_shfl(mask, m1, base + 1), xy = team_shfl(mask, m1, base + 3);
-  const F t2 = mul_small(team_shfl(mask, m1, base + 2), b3);  // b3 Z^2
+  const auto m1 = tm.piece(r == 2 ? a.Z : r >= 3 ? a.X : a.Y, r == 0 || r >= 3 ? a.Y : a.Z);
+  const F t0 = tm.product(m1, 0), t1 = tm.product(m1, 1), xy = tm.product(m1, 3);
+  const F t2 = mul_small(tm.product(m1, 2), b3);  // b3 Z^2
   const F z8 = F::dbl(F::dbl(F::dbl(t0)));                    // 8 Y^2
   const F y3 = F::add(t0, t2);
   const F t0m = F::sub(t0, F::add(F::dbl(t2), t2));           // Y^2 - 3 b3 Z^2
   // round 2:  t2 z8 | t1 z8 | t0m y3 | t0m xy
-  const F m2 = F::mul(r == 0 ? t2 : r == 1 ? t1 : t0m, r <= 1 ? z8 : r == 2 ? y3 : xy);
+  const auto m2 = tm.piece(r == 0 ? t2 : r == 1 ? t1 : t0m, r <= 1 ? z8 : r == 2 ? y3 : xy);
   Proj<F> o;
-  o.Y = F::add(team_shfl(mask, m2, base), team_shfl(mask, m2, base + 2));
-  o.Z = team_shfl(mask, m2, base + 1);
-  o.X = F::dbl(team_shfl(mask, m2, base + 3));
+  o.Y = F::add(tm.product(m2, 0), tm.product(m2, 2));
+  o.Z = tm.product(m2, 1);
+  o.X = F::dbl(tm.product(m2, 3));
   return o;
 }
 
 // two XYZZ values -> projective in ONE round: (X ZZZ : Y ZZ : ZZ ZZZ); XYZZ infinity (ZZ = 0) -> (0 : 1 : 0)
 template <class F>
 __device__ __noinline__ void oct_from_xyzz2(const XYZZ<F>& a, const XYZZ<F>& b, Proj<F>& pa, Proj<F>& pb) {
-  const Octet tm;
-  const int r = tm.role, base = tm.base;
-  const unsigned mask = tm.mask;
+  const ProjTeam<F> tm;
+  const int r = tm.role;
   const bool second = r >= 3 && r < 6;
   const XYZZ<F>& s = second ? b : a;
   const int k = second ? r - 3 : (r < 3 ? r : 0);
-  const F m = F::mul(k == 0 ? s.X : k == 1 ? s.Y : s.ZZ, k == 1 ? s.ZZ : s.ZZZ);
-  pa.X = team_shfl(mask, m, base); pa.Y = team_shfl(mask, m, base + 1); pa.Z = team_shfl(mask, m, base + 2);
-  pb.X = team_shfl(mask, m, base + 3); pb.Y = team_shfl(mask, m, base + 4); pb.Z = team_shfl(mask, m, base + 5);
+  const auto m = tm.piece(k == 0 ? s.X : k == 1 ? s.Y : s.ZZ, k == 1 ? s.ZZ : s.ZZZ);
+  pa.X = tm.product(m, 0); pa.Y = tm.product(m, 1); pa.Z = tm.product(m, 2);
+  pb.X = tm.product(m, 3); pb.Y = tm.product(m, 4); pb.Z = tm.product(m, 5);
   if (a.is_inf()) { pa.X = F::zero(); pa.Y = F::one(); pa.Z = F::zero(); }
   if (b.is_inf()) { pb.X = F::zero(); pb.Y = F::one(); pb.Z = F::zero(); }
 }
@@ -147,17 +181,16 @@ __device__ __noinline__ void oct_from_xyzz2(const XYZZ<F>& a, const XYZZ<F>& b, 
 // projective -> XYZZ (X Z : Y Z^2 : Z^2 : Z^3) for the callers that exchange projective partial sums as XYZZ
 template <class F>
 __device__ __noinline__ XYZZ<F> oct_to_xyzz(const Proj<F>& a) {
-  const Octet tm;
-  const int r = tm.role, base = tm.base;
-  const unsigned mask = tm.mask;
-  const F m1 = F::mul(r == 0 ? a.X : a.Z, a.Z);  // X Z | Z^2
-  const F xz = team_shfl(mask, m1, base), zz = team_shfl(mask, m1, base + 1);
-  const F m2 = F::mul(r == 0 ? a.Y : a.Z, zz);   // Y Z^2 | Z^3
+  const ProjTeam<F> tm;
+  const int r = tm.role;
+  const auto m1 = tm.piece(r == 0 ? a.X : a.Z, a.Z);  // X Z | Z^2
+  const F xz = tm.product(m1, 0), zz = tm.product(m1, 1);
+  const auto m2 = tm.piece(r == 0 ? a.Y : a.Z, zz);   // Y Z^2 | Z^3
   XYZZ<F> o;
   o.X = xz;
-  o.Y = team_shfl(mask, m2, base);
+  o.Y = tm.product(m2, 0);
   o.ZZ = zz;
-  o.ZZZ = team_shfl(mask, m2, base + 1);
+  o.ZZZ = tm.product(m2, 1);
   if (a.is_inf()) o = XYZZ<F>::inf();
   return o;
 }
@@ -196,13 +229,16 @@ __device__ __forceinline__ void oct_load2(const MixedArray<F>& in, uint64_t i, u
 struct OctLane {
   uint64_t oct, nocts;
   bool lead;
+  int lanes;
   template <class F>
   __device__ __forceinline__ OctLane(const TailLane<F>& tl) {
-    oct = tl.vwarp * 4 + (tl.lane >> 3);
-    nocts = tl.nvwarps * 4;
-    lead = (tl.lane & 7) == 0;
+    constexpr int LANES = ProjTeam<F>::LANES;
+    lanes = LANES;
+    oct = tl.vwarp * (32 / LANES) + (tl.lane / LANES);
+    nocts = tl.nvwarps * (32 / LANES);
+    lead = (tl.lane % LANES) == 0;
   }
-  // a level runs on 8-lane teams while that takes at most four rounds
+  // a level runs on the projective teams while that takes at most four rounds
   __device__ __forceinline__ bool fits(uint64_t items) const { return items <= 4 * nocts; }
 };
 
@@ -222,15 +258,8 @@ __device__ __forceinline__ void tailp_pair_level(const TailLane<F>& tl, const Oc
     }
     if (n0) out0.xyzz = false;
     if (n1) out1.xyzz = false;
-  } else {
-    for (uint64_t t = tl.thread(); t < n0 + n1; t += tl.nthreads()) {
-      const bool second = t >= n0;
-      const uint64_t i = second ? t - n0 : t;
-      const XYZZ<F>* in = second ? in1.p : in0.p;
-      XYZZ<F> acc = in[2 * i];
-      acc.add(in[2 * i + 1]);
-      (second ? out1.p : out0.p)[i] = acc;
-    }
+  } else {  // too wide: XYZZ, in the form msm_tail would pick for this width
+    tail_pair_level<F>(tl, in0.p, out0.p, n0, in1.p, out1.p, n1);
     if (n0) out0.xyzz = true;
     if (n1) out1.xyzz = true;
   }
@@ -258,12 +287,8 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, 
   uint64_t r_len = a.r_len, c_len = a.c_len;
 
   if (a.first_stage <= TAIL_FOLD && a.last_stage >= TAIL_FOLD) {
-    // in place on the XYZZ task partials (the wide kernels read them too): 4-lane XYZZ teams as in msm_tail
-    const uint32_t max_nt = *a.max_nt, ntasks = *a.ntasks_ptr;
-    for (uint32_t stride = 1; stride < max_nt; stride <<= 1) {
-      tail_fold_level<F, 4>(tl, a, stride, ntasks);
-      grid_sync(a.barrier);
-    }
+    // in place on the XYZZ task partials (the wide kernels read them too): XYZZ teams as in msm_tail
+    tail_fold_xyzz<F>(tl, a);
   }
   if (a.first_stage <= TAIL_BUCKET_PAIRS && a.last_stage >= TAIL_BUCKET_PAIRS) {
     const uint64_t Lr = a.Cn >= 2 ? a.Cn / 2 : 1, Lc = a.R >= 2 ? a.R / 2 : 1;
@@ -288,10 +313,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, 
       }
       rin.xyzz = cin.xyzz = false;
     } else {
-      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
-        const bool second = t0 >= jr.total;
-        msm_bucket_pair_thread<F>(second ? jc : jr, a.nb, a.task_first, a.partial, second ? t0 - jr.total : t0);
-      }
+      tail_bucket_pairs_xyzz<F>(tl, a, jr, jc);
     }
     r_len = Lr;
     c_len = Lc;
@@ -333,10 +355,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, 
     } else {
       const WeightedJob<F> wr{rin.p, rout.p, a.R, total_r, 0u};
       const WeightedJob<F> wc{cin.p, cout.p, a.Cn, total_c, 1u};
-      for (uint64_t t0 = tl.thread(); t0 < total; t0 += tl.nthreads()) {
-        const bool second = t0 >= wr.total;
-        msm_weighted_chunk_thread<F>(second ? wc : wr, second ? t0 - wr.total : t0);
-      }
+      tail_weighted_xyzz<F>(tl, wr, wc);
       rout.xyzz = cout.xyzz = true;
     }
     { MixedArray<F> t = rin; rin = rout; rout = t; }
@@ -372,13 +391,13 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, 
       }
       group_xyzz = a.last_stage < TAIL_FINISH;
     } else {
-      for (uint64_t g = tl.thread(); g < a.groups; g += tl.nthreads()) msm_group_combine_thread<F>(a.h, rin.p, cin.p, a.group_out, g);
+      tail_combine_xyzz<F>(tl, a, rin.p, cin.p);
     }
     if (a.last_stage >= TAIL_FINISH) grid_sync(a.barrier);
   }
   if (a.first_stage <= TAIL_FINISH && a.last_stage >= TAIL_FINISH) {
-    // one MSM per WARP (its first 8 lanes): the inversion is a data-dependent loop
-    if (tl.lane < 8) {
+    // one MSM per WARP (its first team): the inversion is a data-dependent loop
+    if (tl.lane < ProjTeam<F>::LANES) {
       const Proj<F>* gp = reinterpret_cast<const Proj<F>*>(a.group_out);
       for (uint64_t m = tl.vwarp; m < a.batch; m += tl.nvwarps) {
         auto load = [&](uint64_t idx) -> Proj<F> {
@@ -416,6 +435,35 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) msm_tail_proj(TailArgs<F> a, 
       }
     }
   }
+}
+
+// kzg_gpu_microbench kinds 10..13: one dependent chain of G2 additions on 16-lane XYZZ teams (10), 4-lane XYZZ teams (11),
+// whole-warp projective teams (12), and of G1 additions on 8-lane projective teams (13), msm_tail configuration
+template <class F1, class F2>
+__global__ void __launch_bounds__(TAIL_THREADS, 1) bench_latency_chain_g2(int kind, int iters, uint32_t seed, B3 b3, uint32_t* sink) {
+  F1 t = F1::one();
+  t.v[0] ^= (seed & 0xffu) + 3u;
+  const F1 u = F1::mul(t, F1::r2()), v = F1::sqr(u), w = F1::mul(u, v);
+  uint32_t o = 0;
+  if (kind == 13) {
+    Proj<F1> acc{u, v, w}, p{w, u, v};
+    for (int it = 0; it < iters; it++) acc = oct_add<F1>(acc, p, b3);
+    o = acc.X.v[0] ^ acc.Z.v[1];
+  } else if (kind == 12) {
+    Proj<F2> acc{F2{u, v}, F2{v, w}, F2{w, u}}, p{F2{w, v}, F2{u, w}, F2{v, u}};
+    for (int it = 0; it < iters; it++) acc = oct_add<F2>(acc, p, b3);
+    o = acc.X.a.v[0] ^ acc.Z.b.v[1];
+  } else {
+    XYZZ<F2> acc, p;
+    acc.X = F2{u, v}; acc.Y = F2{v, w}; acc.ZZ = F2{w, u}; acc.ZZZ = F2{u, w};
+    p.X = F2{w, v}; p.Y = F2{u, u}; p.ZZ = F2{v, u}; p.ZZZ = F2{w, w};
+    for (int it = 0; it < iters; it++) {
+      if (kind == 10) acc = team_add<F2, 16>(acc, p);
+      else acc = team_add<F2, 4>(acc, p);
+    }
+    o = acc.X.a.v[0] ^ acc.ZZZ.b.v[1];
+  }
+  if (o == 0x12345678u) sink[0] = o;
 }
 
 }  // namespace kzgb200

@@ -60,12 +60,20 @@ template <class F>
 __device__ __forceinline__ F team_piece(const Team<F, 4>&, const F& x, const F& y) {
   return F::mul(x, y);  // the whole product (for Fp2: three dependent Fp products in this lane)
 }
+// 16 lanes: part 0 / 1 / 2 of a role multiply a a' / b b' / (a + b)(a' + b'); the Karatsuba recombination is done ONCE
+// here, by the role's own lanes (two shuffles and two subtractions for all four roles at the same time), so that
+// the piece of part 0 is the real and the piece of part 1 the imaginary component of the role's product — a consumer
+// then fetches a product with two shuffles and no arithmetic (recombining at every consumer cost ~0.5 us per round).
 template <class P>
 __device__ __forceinline__ Field<P> team_piece(const Team<Field2<P>, 16>& tm, const Field2<P>& x, const Field2<P>& y) {
   using Base = Field<P>;
   const Base u = tm.part == 0 ? x.a : tm.part == 1 ? x.b : Base::add(x.a, x.b);
   const Base v = tm.part == 0 ? y.a : tm.part == 1 ? y.b : Base::add(y.a, y.b);
-  return Base::mul(u, v);
+  const Base m = Base::mul(u, v);
+  const Base other = team_shfl(tm.mask, m, tm.lane ^ 1);         // part 0 gets b b', part 1 gets a a'
+  const Base third = team_shfl(tm.mask, m, (tm.lane & ~3) | 2);  // (a + b)(a' + b')
+  // part 0:  a a' - b b' - 0 ;  part 1:  (a + b)(a' + b') - a a' - b b'   (parts 2 and 3: unused)
+  return Base::sub(Base::sub(tm.part == 0 ? m : third, other), tm.part == 0 ? Base::zero() : m);
 }
 // ... and the complete product of role r, on every lane of the team
 template <class F>
@@ -74,10 +82,7 @@ __device__ __forceinline__ F team_product(const Team<F, 4>& tm, const F& piece, 
 }
 template <class P>
 __device__ __forceinline__ Field2<P> team_product(const Team<Field2<P>, 16>& tm, const Field<P>& piece, int r) {
-  using Base = Field<P>;
-  const Base t0 = team_shfl(tm.mask, piece, tm.base + 4 * r), t1 = team_shfl(tm.mask, piece, tm.base + 4 * r + 1),
-             t2 = team_shfl(tm.mask, piece, tm.base + 4 * r + 2);
-  return Field2<P>{Base::sub(t0, t1), Base::sub(Base::sub(t2, t0), t1)};  // (a a' - b b') + ((a + b)(a' + b') - a a' - b b') i
+  return Field2<P>{team_shfl(tm.mask, piece, tm.base + 4 * r), team_shfl(tm.mask, piece, tm.base + 4 * r + 1)};
 }
 
 // a + b (add-2008-s, same case analysis as XYZZ::add); a, b and the result are replicated on the team

@@ -74,6 +74,44 @@ def test_tail_and_fused_sort_give_the_same_bytes(cname):
     ctx.close()
 
 
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_g2_projective_tail_gives_the_same_bytes(cname):
+    """"tail_proj" = 2: the G2 reduction tail in complete projective coordinates on whole-warp teams (msm_tail_proj.cuh,
+    ProjTeam<Fp2>) against the XYZZ team tail, the round-1 multi-launch path and the oracle."""
+    C = get_curve(cname)
+    ctx = kzg_b200.Context(cname, 0)
+    rng = random.Random(99 + C.id)
+    s = rng.randrange(C.r)
+    nmax = 4097
+    for pre in (2, 0):
+        ctx.set_option("precompute", pre)
+        ctx.setup_powers(s, nmax)
+        cases = [("n%d" % n, [rng.randrange(C.r) for _ in range(n)]) for n in (1, 2, 3, 129, 1025, nmax)]
+        cases += [("ones", [1] * 600), ("rm1", [C.r - 1] * 600), ("zeros", [0] * 50),
+                  ("half_zero", [rng.randrange(C.r) if i & 1 else 0 for i in range(nmax)]),
+                  ("single", [0] * 999 + [rng.randrange(1, C.r)])]
+        for name, sc in cases:
+            raw = C.scalars_to_bytes(sc)
+            ctx.set_option("tail", 1)
+            ctx.set_option("tail_proj", 2)
+            got = ctx.msm_g2(raw, len(sc))
+            ctx.set_option("tail_proj", 1)
+            assert ctx.msm_g2(raw, len(sc)) == got, (pre, name)
+            ctx.set_option("tail", 0)
+            assert ctx.msm_g2(raw, len(sc)) == got, (pre, name)
+            if len(sc) <= 1025:
+                want = C.mul(C.poly_eval(sc, s), C.g2, g2=True)
+                assert got == (C.g2_to_octet(want)[1:], want is None), (pre, name)
+        # the sum is the point at infinity: c0 + c1 s = 0
+        sc = [(C.r - 7 * s % C.r) % C.r, 7]
+        ctx.set_option("tail", 1)
+        ctx.set_option("tail_proj", 2)
+        xy, inf = ctx.msm_g2(C.scalars_to_bytes(sc), 2)
+        assert inf and xy == bytes(len(xy)), pre
+        ctx.set_option("tail_proj", 1)
+    ctx.close()
+
+
 def test_tail_at_2_16_and_2_18():
     """sizes where part of the reduction is still wide launches and the rest runs in the tail kernel"""
     C = get_curve("bls12381")

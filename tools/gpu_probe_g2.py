@@ -33,12 +33,16 @@ for cname in ("bls12381", "bn254"):
     sc = rng.integers(0, 256, size=(4097, ctx.SB), dtype=np.uint8)
     sc[:, ctx.SB - 1] &= 0x0F
     raw = sc.tobytes()
-    for proj in (1, 0):
+    for proj in (2, 1):
         ctx.set_option("tail_proj", proj)
         for count in (2, 129, 1025, 4097):
             for grp, fn in (("g2", ctx.msm_g2), ("g1", ctx.msm_g1)):
                 ms = best(lambda: fn(raw[:count * ctx.SB], count))
                 out["%s_%s_%d_proj%d" % (cname, grp, count, proj)] = {"ms": round(ms, 4), "phases": ctx.phase_times()}
+    ctx.set_option("tail_proj", 1)
+    out[cname + "_latency_us"] = {name: round(1e6 / ctx.microbench(kind), 3) for kind, name in
+                                  ((10, "g2_add_xyzz_16lane"), (11, "g2_add_xyzz_4lane"), (12, "g2_add_proj_32lane"),
+                                   (13, "g1_add_proj_8lane"), (5, "g1_add_xyzz_4lane"), (7, "fp_modmul"))}
     ctx.close()
     ts = []
     for rep in range(4):
