@@ -1,5 +1,5 @@
 set -u
-T=${TAG:-r2x}
+T=${TAG:-r2y}
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests/test_gpu_parity.py tests/test_gpu_tail_and_group.py tests/test_gpu_kat_large.py -x -q --timeout 900 > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?"
 tail -8 gpurun_out/${T}_pytest.log
