@@ -7,7 +7,10 @@ r = list(csv.reader(rows))
 hdr = r[0]; ki = hdr.index('Kernel Name'); vi = hdr.index('Metric Value'); ui = hdr.index('Metric Unit')
 ks = [(re.sub(r'^void ', '', re.sub(r'[<(].*', '', x[ki])).split('::')[-1], float(x[vi].replace(',', '')) / (1000 if x[ui] == 'ns' else 1)) for x in r[1:]]
 last = [i for i, k in enumerate(ks) if k[0] == 'msm_digits'][-1]
-end = next(i for i in range(last, len(ks)) if ks[i][0] == 'msm_finish') + 1
+# the pass ends with msm_finish (multi-launch path) or with the last msm_tail / msm_tail_proj launch before another kernel family
+end = last + 1
+while end < len(ks) and ks[end][0].startswith(('msm_', 'scan_')) and ks[end][0] != 'msm_digits':
+    end += 1
 ks = ks[:end]
 agg = OrderedDict(); tot = 0
 for n, v in ks[last:]:
