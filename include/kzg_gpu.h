@@ -75,6 +75,8 @@ void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
  * kzg_gpu_msm_partial_device — the point-range split folds and normalises once, after the exchange).
  * "tail" (1: the sort and the narrow end of the reduction run in two persistent cooperative kernels), "tail_proj" (1: that
  * end uses complete projective formulas on 8-lane teams for G1; 2: also for G2, on whole-warp teams), "table_pad" (experiment: 128-byte window-table entries),
+ * "table_ladder" (1: a large SRS also gets window tables of its first 8192 and 131072 points with window widths that suit
+ * those sizes, used by MSMs that fit — a small commitment does not walk the bucket reduction of the big table),
  * "barrier_sleep" (ns between polls of the grid barrier).
  * Takes effect at the next srs_load / setup_powers / MSM. */
 int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value);

@@ -74,7 +74,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1, opt_table_pad = 0, opt_barrier_sleep = 64, opt_tail_proj = 1;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1, opt_table_pad = 0, opt_barrier_sleep = 64, opt_tail_proj = 1, opt_table_ladder = 1;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -163,6 +163,15 @@ struct Ctx final : kzg_gpu_ctx {
   DevBuf g1_table, g2_table; // per-SRS window tables T[w][i] = 2^(c*w) * G_i (row 0 = the SRS itself)
   int table_c = 0, table_W = 0;
   size_t g1_point_stride = sizeof(Affine<Fp>);
+  // The table ladder: window tables of PREFIXES of a large SRS with the window width that suits the prefix.  The window
+  // width of the main table is chosen for srs_n (c = 20: 2^19 buckets at 2^20 points), and an MSM walks the whole bucket
+  // reduction of that width however few terms it has — a degree-4096 commitment against a 2^20-point setup (the
+  // reference's benchmark.cpp commits polynomials of degree 1024 and up against one 10.4 M-term setup) would cost
+  // ~1.2 ms instead of the 0.46 ms it costs against a 4096-point one.  MSMs over points [0, n_k) use rung k.
+  struct TableRung { DevBuf buf; uint64_t n = 0; int c = 0, W = 0; };
+  static constexpr int N_RUNGS = 2;
+  static constexpr uint64_t RUNG_POINTS[N_RUNGS] = {8192, 131072};
+  TableRung rungs[N_RUNGS];
   // fixed-base tables of the generators
   // (constants of the curve: built once per process and device, shared by every context, never freed)
   struct FbShared { Affine<Fp>* t1 = nullptr; Affine<Fp2>* t2 = nullptr; };
@@ -247,6 +256,7 @@ struct Ctx final : kzg_gpu_ctx {
     g2_table_pending = false;
     g1_table.release();
     g2_table.release();
+    for (TableRung& rg : rungs) { rg.buf.release(); rg.n = 0; }
     table_c = table_W = 0;
     if (srs_n == 0) return KZG_GPU_OK;
     if (!opt_precompute) return reserve_scratch();
@@ -266,6 +276,24 @@ struct Ctx final : kzg_gpu_ctx {
       msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
           srs_n, srs_n, c, W, g1.as<Affine<Fp>>(), g1_table.as<Affine<Fp>>(), g1_point_stride);
     LAUNCHED();
+    for (int k = 0; k < N_RUNGS; k++) {
+      TableRung& rg = rungs[k];
+      rg.buf.release();
+      rg.n = 0;
+      const uint64_t nk = RUNG_POINTS[k];
+      if (!opt_table_ladder || opt_window_bits || srs_n < 4 * nk) continue;
+      const int ck = pick_table_c(nk), Wk = (C::SCALAR_BITS + 1 + ck - 1) / ck;
+      if (ck >= c || Wk > MAXW) continue;
+      CK(rg.buf.ensure((size_t)Wk * nk * sizeof(Affine<Fp>)));
+      if (nk <= TABLE_TEAM_MAX_POINTS)
+        msm_precompute_table_team<Fp, MAXW><<<(unsigned)((TeamWidth<Fp>::LANES * nk + 127) / 128), 128, 0, stream>>>(
+            nk, nk, ck, Wk, g1.as<Affine<Fp>>(), rg.buf.template as<Affine<Fp>>(), sizeof(Affine<Fp>));
+      else
+        msm_precompute_table<Fp, MAXW><<<(unsigned)((nk + 127) / 128), 128, 0, stream>>>(
+            nk, nk, ck, Wk, g1.as<Affine<Fp>>(), rg.buf.template as<Affine<Fp>>(), sizeof(Affine<Fp>));
+      LAUNCHED();
+      rg.n = nk; rg.c = ck; rg.W = Wk;
+    }
     CK(cudaStreamSynchronize(stream));
     table_c = c;
     table_W = W;
@@ -447,8 +475,9 @@ struct Ctx final : kzg_gpu_ctx {
   // Enqueue one Pippenger pass for `batch` MSMs of `count` scalars (device-resident bytes).
   // Leaves affine bytes + flags in out_bytes/out_inf and the projective result of each MSM in out_xyzz.
   template <class F>
+  // table_rows: points per row of `table` (0: srs_n — the main table; otherwise a rung of the table ladder)
   int enqueue_msm(const Affine<F>* bases, const Affine<F>* table, int tc, const uint8_t* d_scalars, uint64_t count,
-                  uint64_t batch, uint64_t base_offset, bool reserve_only = false) {
+                  uint64_t batch, uint64_t base_offset, bool reserve_only = false, uint64_t table_rows = 0) {
     MsmShape sh;
     const bool precomp = table != nullptr;
     sh.c = precomp ? tc : (opt_window_bits ? opt_window_bits : pick_plain_c(count));
@@ -458,7 +487,7 @@ struct Ctx final : kzg_gpu_ctx {
     sh.groups_per_msm = precomp ? 1 : sh.W;
     sh.n = count;
     sh.batch = batch;
-    sh.table_stride = srs_n;
+    sh.table_stride = table_rows ? table_rows : srs_n;
     sh.base_offset = base_offset;
     const uint64_t records = count * batch * (uint64_t)sh.W;
     // task length: long enough to amortise the fold, short enough that a small MSM still fills the machine
@@ -469,9 +498,10 @@ struct Ctx final : kzg_gpu_ctx {
     int levels = 0;
     if (std::is_same<F, Fp>::value) levels = opt_affine_levels >= 0 ? opt_affine_levels : 0;
     if (g1_point_stride != sizeof(Affine<Fp>)) levels = 0;  // the affine levels read the table at its natural stride
+    if (table_rows) levels = 0;
     sh.chunk = opt_task_chunk ? std::min(opt_task_chunk, MSM_MAX_CHUNK)
                               : (int)std::min<uint64_t>(128, std::max<uint64_t>(4, (records >> levels) / 65536));
-    if (records >= (1ull << 31) || (precomp && (uint64_t)sh.W * srs_n >= (1ull << 31))) return KZG_GPU_ERR_ARG;
+    if (records >= (1ull << 31) || (precomp && (uint64_t)sh.W * sh.table_stride >= (1ull << 31))) return KZG_GPU_ERR_ARG;
     const uint64_t nbuckets = sh.total_buckets();
     const uint64_t max_tasks = ((records >> levels) + nbuckets) / sh.chunk + nbuckets + 1;
     const uint64_t groups = sh.total_groups();
@@ -594,7 +624,7 @@ struct Ctx final : kzg_gpu_ctx {
     phase_mark(1);
     {
       unsigned grid = (unsigned)std::min<uint64_t>((max_tasks + 127) / 128, (uint64_t)1 << 30);
-      const size_t pt_stride = (precomp && std::is_same<F, Fp>::value && levels == 0) ? g1_point_stride : sizeof(Affine<F>);
+      const size_t pt_stride = (precomp && std::is_same<F, Fp>::value && levels == 0 && !table_rows) ? g1_point_stride : sizeof(Affine<F>);
       msm_accumulate<F><<<grid, 128, 0, stream>>>(task_first.as<uint32_t>() + nbuckets, tasks.as<MsmTask>(), seg_sorted,
                                                   seg_pts, partial.as<XYZZ<F>>(), pt_stride);
       LAUNCHED();
@@ -801,7 +831,11 @@ struct Ctx final : kzg_gpu_ctx {
       return KZG_GPU_OK;
     }
     const bool use_table = group == 1 ? g1_table.p != nullptr : g2_table.p != nullptr;
-    const int Wguess = use_table ? table_W : (C::SCALAR_BITS + 8) / 8;
+    const TableRung* rung = nullptr;  // G1: the smallest rung of the table ladder that holds every point of this MSM
+    if (group == 1 && use_table && opt_table_ladder)
+      for (const TableRung& rg : rungs)
+        if (rg.n && base_offset + count <= rg.n) { rung = &rg; break; }
+    const int Wguess = rung ? rung->W : use_table ? table_W : (C::SCALAR_BITS + 8) / 8;
     uint64_t per_pass = do_fetch ? max_batch_per_pass(count, Wguess) : batch;
     // Host scalars of a large batch: split into passes of >= 128 MSMs so that the copy of pass i + 1 (copy stream,
     // second staging buffer) runs under the kernels of pass i; one pass would leave the whole H2D exposed
@@ -866,8 +900,9 @@ struct Ctx final : kzg_gpu_ctx {
       }
       int rc;
       if (group == 1)
-        rc = enqueue_msm<Fp>(g1.as<Affine<Fp>>(), use_table ? g1_table.as<Affine<Fp>>() : nullptr, table_c, d_scal,
-                             count, nb, base_offset);
+        rc = rung ? enqueue_msm<Fp>(g1.as<Affine<Fp>>(), rung->buf.template as<Affine<Fp>>(), rung->c, d_scal, count, nb, base_offset, false, rung->n)
+                  : enqueue_msm<Fp>(g1.as<Affine<Fp>>(), use_table ? g1_table.as<Affine<Fp>>() : nullptr, table_c, d_scal,
+                                    count, nb, base_offset);
       else
         rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), use_table ? g2_table.as<Affine<Fp2>>() : nullptr, table_c, d_scal,
                               count, nb, base_offset);

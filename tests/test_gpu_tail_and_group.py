@@ -112,6 +112,41 @@ def test_g2_projective_tail_gives_the_same_bytes(cname):
     ctx.close()
 
 
+@pytest.mark.parametrize("cname", ["bls12381", "bn254"])
+def test_table_ladder_gives_the_same_bytes(cname):
+    """A large SRS keeps window tables of its first 8192 / 131072 points too (ctx.cuh TableRung); MSMs that fit use them.
+    Same bytes as with the ladder switched off (main table), as the no-table path, and as the oracle."""
+    C = get_curve(cname)
+    ctx = kzg_b200.Context(cname, 0)
+    ctx.set_option("setup_g2", 0)
+    rng = random.Random(123 + C.id)
+    s = rng.randrange(C.r)
+    n = 40000                      # >= 4 * 8192: the first rung exists, the second does not
+    ctx.setup_powers(s, n, want_bytes=False)
+    nb2 = 2 * ctx.M
+    for count, batch, off in ((1, 1, 0), (2, 1, 0), (4097, 1, 0), (8192, 1, 0), (8193, 1, 0), (4097, 3, 0), (100, 1, 8000),
+                              (100, 1, 8150), (500, 2, 7000)):
+        coeffs = [rng.randrange(C.r) for _ in range(count * batch)]
+        raw = C.scalars_to_bytes(coeffs)
+        call = (lambda: ctx.msm_g1_batch(raw, count, batch)) if batch > 1 else (lambda: ctx.msm_g1(raw, count, off))
+        ctx.set_option("table_ladder", 1)
+        got = call()
+        s0 = ctx.msm_stats()
+        ctx.set_option("table_ladder", 0)
+        assert call() == got, (count, batch, off)
+        s1 = ctx.msm_stats()
+        if off + count <= 8192 and cname == "bls12381":
+            assert s0["window_bits"] < s1["window_bits"], (count, s0, s1)   # the rung's narrower windows were used
+        elif off + count <= 8192:  # (BN254: the cost model picks the same width for 8192 and 40000 points: no rung)
+            assert s0["window_bits"] <= s1["window_bits"], (count, s0, s1)
+        else:
+            assert s0["window_bits"] == s1["window_bits"], (count, s0, s1)
+        if count <= 4097 and batch == 1:
+            want = C.mul(C.poly_eval(coeffs, s) * pow(s, off, C.r) % C.r, C.g1)
+            assert got[0] == C.g1_to_octet(want)[1:], (count, off)
+    ctx.close()
+
+
 def test_tail_at_2_16_and_2_18():
     """sizes where part of the reduction is still wide launches and the rest runs in the tail kernel"""
     C = get_curve("bls12381")
