@@ -343,9 +343,12 @@ struct Ctx final : kzg_gpu_ctx {
   // Size the MSM scratch for one MSM over the whole SRS now, so that the first commitment of each new size does
   // not pay ~20 cudaFree/cudaMalloc pairs (measured: 1.9 ms instead of 1.0 ms for the first degree-4096 commit
   // after a degree-2048 one in the reference's benchmark.cpp).  Larger batches still grow the buffers on demand.
+  // A very large SRS reserves for MSMs of up to 2^20 terms (0.3 GB): the reference's benchmark.cpp commits
+  // polynomials of degree 1024 .. 2^23 against one 10.4 M-term setup, and growing twenty buffers of tens of MB in front
+  // of each new size cost 10-20 ms per row (profiles/r2common_benchmark_common_bls12381.txt).
   int reserve_scratch() {
-    if (srs_n == 0 || srs_n > (1ull << 22)) return KZG_GPU_OK;
-    const uint64_t cnt = srs_n;
+    if (srs_n == 0) return KZG_GPU_OK;
+    const uint64_t cnt = std::min<uint64_t>(srs_n, srs_n > (1ull << 22) ? (1ull << 20) : srs_n);
     CK(scal.ensure(cnt * (size_t)SB));
     int rc = enqueue_msm<Fp>(g1.as<Affine<Fp>>(), g1_table.p ? g1_table.as<Affine<Fp>>() : nullptr, table_c, nullptr, cnt, 1, 0, true);
     if (rc) return rc;

@@ -19,6 +19,7 @@
 // a side table keyed by the object's address and validated by a fingerprint of its SRS.
 #include <kzg.h>
 
+#include <algorithm>
 #include <array>
 #include <cstdint>
 #include <cstdlib>
@@ -158,6 +159,11 @@ struct ByContent {
 std::mutex g_mu;
 std::map<const void*, ByAddress> g_by_address;
 std::map<Digest, ByContent> g_by_content;
+struct ByRaw {
+  std::weak_ptr<Side> side;
+  Digest content;
+};
+std::map<Digest, ByRaw> g_by_raw;  // in-memory fingerprint (raw_digest_of) -> resident copy: a shortcut to g_by_content
 uint64_t g_clock = 0;
 
 size_t cache_capacity() {
@@ -178,19 +184,93 @@ int devices_for(size_t n) {
   // is split by point range over all visible devices (kzg_gpu_group_msm_g1: 3.6x on 8 GPUs at 2^20, 6.4x at 2^22).
   return n >= ((size_t)1 << 20) ? visible : 1;
 }
-Digest digest_of(const std::vector<uint8_t>& b1, const std::vector<uint8_t>& b2) {
-  Digest d = {0xcbf29ce484222325ull, 0x84222325cbf29ce4ull};  // two FNV-1a style lanes over different strides
-  auto feed = [&](const std::vector<uint8_t>& v) {
-    for (size_t i = 0; i < v.size(); i++) {
-      d[0] = (d[0] ^ v[i]) * 0x100000001b3ull;
-      d[1] = (d[1] ^ (uint64_t)(v[i] + 0x9e) ^ (d[0] >> 29)) * 0x9e3779b97f4a7c15ull;
-    }
+// 128-bit fingerprint of a byte range: 64-bit words through two multiply-xorshift lanes.  Long inputs are cut into
+// pieces hashed side by side on the host cores and the piece digests are folded in order (a 10.4 M-point SRS is 3 GB:
+// a byte-at-a-time serial loop took 4.5 s of the constructor).
+Digest digest_bytes(const uint8_t* p, size_t len) {
+  Digest d = {0xcbf29ce484222325ull ^ len, 0x84222325cbf29ce4ull + len * 0x9e3779b97f4a7c15ull};
+  auto mix = [&](uint64_t w) {
+    d[0] = (d[0] ^ w) * 0x100000001b3ull;
+    d[0] ^= d[0] >> 29;
+    d[1] = (d[1] + w) * 0x9e3779b97f4a7c15ull;
+    d[1] ^= d[1] >> 32;
   };
-  feed(b1);
-  feed(b2);
-  d[0] ^= b1.size();
-  d[1] ^= b2.size() * 0x9e3779b97f4a7c15ull;
+  size_t i = 0;
+  for (; i + 8 <= len; i += 8) {
+    uint64_t w;
+    memcpy(&w, p + i, 8);
+    mix(w);
+  }
+  uint64_t tail = 0;
+  if (i < len) memcpy(&tail, p + i, len - i);
+  mix(tail ^ ((uint64_t)(len - i) << 56));
   return d;
+}
+template <class PieceFn>  // piece(k, lo, hi) -> Digest of items [lo, hi)
+Digest digest_in_pieces(size_t n_items, size_t min_items_per_piece, PieceFn piece) {
+  unsigned hw = std::thread::hardware_concurrency();
+  const size_t np = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(hw ? hw : 4, 16), n_items / std::max<size_t>(1, min_items_per_piece)));
+  std::vector<Digest> part(np);
+  std::vector<std::thread> pool;
+  for (size_t k = 1; k < np; k++) pool.emplace_back([&, k] { part[k] = piece(n_items * k / np, n_items * (k + 1) / np); });
+  part[0] = piece(0, n_items / np);
+  for (auto& th : pool) th.join();
+  return digest_bytes(reinterpret_cast<const uint8_t*>(part.data()), part.size() * sizeof(Digest));
+}
+Digest digest_of(const std::vector<uint8_t>& b1, const std::vector<uint8_t>& b2) {
+  auto of = [](const std::vector<uint8_t>& v) {
+    return digest_in_pieces(v.size(), (size_t)1 << 20, [&](size_t lo, size_t hi) { return digest_bytes(v.data() + lo, hi - lo); });
+  };
+  const Digest a = of(b1), b = of(b2);
+  const uint64_t both[6] = {a[0], a[1], b[0], b[1], (uint64_t)b1.size(), (uint64_t)b2.size()};
+  return digest_bytes(reinterpret_cast<const uint8_t*>(both), sizeof both);
+}
+// Fingerprint of the points AS THEY LIE IN MEMORY (limbs and excess words of every coordinate, no padding): copies of
+// a trusted_setup and the object a constructor just filled have the same one, and computing it needs no field
+// arithmetic.  It is only ever used to FIND the resident copy of an equal object sooner (serialising 10.4 M points for
+// the content fingerprint took 15 s in front of the first create_commit of a copied setup); two equal setups whose
+// limbs differ (MIRACL's residues are not unique) simply miss here and are matched by content.
+Digest raw_digest_of(const std::vector<ECP>& g1, const std::vector<ECP2>& g2) {
+  auto fp = [](const FP& f, uint64_t* w) {
+    memcpy(w, f.g, sizeof f.g);
+    w[sizeof f.g / 8] = (uint64_t)(uint32_t)f.XES;
+  };
+  constexpr size_t FW = sizeof(((FP*)nullptr)->g) / 8 + 1;
+  const Digest a = digest_in_pieces(g1.size(), 4096, [&](size_t lo, size_t hi) {
+    std::vector<uint64_t> buf(3 * FW * 256);
+    Digest d = {hi - lo, lo};
+    for (size_t i = lo; i < hi;) {
+      const size_t m = std::min<size_t>(256, hi - i);
+      for (size_t j = 0; j < m; j++) {
+        const ECP& p = g1[i + j];
+        fp(p.x, &buf[(3 * j) * FW]); fp(p.y, &buf[(3 * j + 1) * FW]); fp(p.z, &buf[(3 * j + 2) * FW]);
+      }
+      const Digest e = digest_bytes(reinterpret_cast<const uint8_t*>(buf.data()), m * 3 * FW * 8);
+      d[0] = (d[0] ^ e[0]) * 0x100000001b3ull;
+      d[1] = (d[1] + e[1]) * 0x9e3779b97f4a7c15ull;
+      i += m;
+    }
+    return d;
+  });
+  const Digest b = digest_in_pieces(g2.size(), 4096, [&](size_t lo, size_t hi) {
+    std::vector<uint64_t> buf(6 * FW * 256);
+    Digest d = {hi - lo, lo};
+    for (size_t i = lo; i < hi;) {
+      const size_t m = std::min<size_t>(256, hi - i);
+      for (size_t j = 0; j < m; j++) {
+        const ECP2& q = g2[i + j];
+        uint64_t* o = &buf[6 * j * FW];
+        fp(q.x.a, o); fp(q.x.b, o + FW); fp(q.y.a, o + 2 * FW); fp(q.y.b, o + 3 * FW); fp(q.z.a, o + 4 * FW); fp(q.z.b, o + 5 * FW);
+      }
+      const Digest e = digest_bytes(reinterpret_cast<const uint8_t*>(buf.data()), m * 6 * FW * 8);
+      d[0] = (d[0] ^ e[0]) * 0x100000001b3ull;
+      d[1] = (d[1] + e[1]) * 0x9e3779b97f4a7c15ull;
+      i += m;
+    }
+    return d;
+  });
+  const uint64_t both[6] = {a[0], a[1], b[0], b[1], (uint64_t)g1.size(), (uint64_t)g2.size()};
+  return digest_bytes(reinterpret_cast<const uint8_t*>(both), sizeof both);
 }
 std::vector<uint8_t> stamp_of(const std::vector<ECP>& g1, const std::vector<ECP2>& g2) {
   std::vector<uint8_t> s(2 * G1_BYTES + 2 * G2_BYTES, 0);
@@ -227,6 +307,8 @@ void remember_locked(const void* self, const SidePtr& side, const Digest& digest
   if (g_by_address.size() > 256)
     for (auto it = g_by_address.begin(); it != g_by_address.end();)
       it = it->second.side.expired() ? g_by_address.erase(it) : std::next(it);
+  for (auto it = g_by_raw.begin(); it != g_by_raw.end();)
+    it = it->second.side.expired() ? g_by_raw.erase(it) : std::next(it);
 }
 // device side of `self`, uploading the SRS the first time (or again if the object at this address changed)
 SidePtr device_of(const void* self, const std::vector<ECP>& g1, const std::vector<ECP2>& g2) {
@@ -242,6 +324,16 @@ SidePtr device_of(const void* self, const std::vector<ECP>& g1, const std::vecto
     }
   }
   const size_t n = g1.size();
+  const Digest raw = raw_digest_of(g1, g2);
+  {
+    auto rh = g_by_raw.find(raw);
+    if (rh != g_by_raw.end())
+      if (SidePtr side = rh->second.side.lock())
+        if (side->n == n) {  // a copy of (or the very object behind) a resident setup: nothing to serialise
+          remember_locked(self, side, rh->second.content, std::move(stamp));
+          return side;
+        }
+  }
   std::vector<uint8_t> b1(n * (size_t)G1_BYTES), b2(g2.size() == n ? n * (size_t)G2_BYTES : 0);
   {
     auto pack = [&](size_t lo, size_t hi) {
@@ -266,12 +358,14 @@ SidePtr device_of(const void* self, const std::vector<ECP>& g1, const std::vecto
   if (hit != g_by_content.end() && hit->second.side->n == n) {  // a copy of a setup that is already resident
     SidePtr side = hit->second.side;
     remember_locked(self, side, digest, std::move(stamp));
+    g_by_raw[raw] = ByRaw{side, digest};
     return side;
   }
   SidePtr side = new_side(n);
   int rc = kzg_gpu_group_srs_load(side->group, n, b1.data(), b2.empty() ? nullptr : b2.data());
   if (rc) throw std::runtime_error(std::string("kzg gpu: srs_load failed: ") + kzg_gpu_group_last_error(side->group));
   remember_locked(self, side, digest, std::move(stamp));
+  g_by_raw[raw] = ByRaw{side, digest};
   return side;
 }
 
@@ -379,8 +473,10 @@ kzg::trusted_setup::trusted_setup(int num_coeff) {
     rebuild(0, n / nt);
     for (auto& th : pool) th.join();
   }
+  const Digest digest = digest_of(b1, b2), raw = raw_digest_of(_G1, _G2);
   std::lock_guard<std::mutex> lock(g_mu);
-  remember_locked(this, side, digest_of(b1, b2), stamp_of(_G1, _G2));
+  remember_locked(this, side, digest, stamp_of(_G1, _G2));
+  g_by_raw[raw] = ByRaw{side, digest};
 }
 
 // trusted_setup(filename): same file format and the same three failure modes as src/trusted_setup.cpp:76-121.
