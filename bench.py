@@ -209,6 +209,13 @@ def scalars_to_ints(arr):
     return [int.from_bytes(raw[i:i + 32], "little") for i in range(0, len(raw), 32)]
 
 
+def _timed(fn):
+    """milliseconds of one host-timed call"""
+    t0 = time.perf_counter()
+    fn()
+    return (time.perf_counter() - t0) * 1e3
+
+
 def fr_eval(ints, s, r, first=0):
     """sum_i ints[i] * s^(first + i) mod r (Horner)."""
     acc = 0
@@ -443,6 +450,45 @@ def run_b200(args):
             assert tot_pt == want, "batched commitments: sum of all commitments differs from [sum_b P_b(s)]G1"
         commit = {"blobs": args.blobs, "blobs_per_gpu": nb, "coeffs": nc, "ms_resident": allmax(min(times[1:])),
                   "ms_e2e": allmax(t_e2e), "ms_prove_e2e": allmax(t_prove), "stats": cstats, "phases": cphases}
+        # ---- the same batch through the DIRECT-LOOKUP table (csrc/msm_direct.cuh; opt-in: tens of GiB of HBM per SRS):
+        # every multiple a digit can select is tabulated, so a commitment is a plain sum of looked-up points.  Outputs
+        # must be byte-identical to the bucket pipeline's, whose checksum of checksums was asserted above.
+        if args.direct_table_gb > 0:
+            dt, d_e2e, d_prove, d_single, b_single, t_build, dstats = [0.0, 0.0, 0.0], 0.0, 0.0, 0.0, 0.0, 0.0, None
+            if nb:
+                one = hb[:nc * 32]
+                ctx.msm_g1(one, nc)
+                b_single = min(_timed(lambda: ctx.msm_g1(one, nc)) for _ in range(7))
+                ctx.set_option("direct_table_gb", args.direct_table_gb)
+                t0 = time.perf_counter()
+                ctx.setup_powers(SECRET, nc + 1, want_bytes=False)
+                t_build = (time.perf_counter() - t0) * 1e3
+                dt = []
+                for it in range(3):
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    flush.zero_()
+                    torch.cuda.synchronize()
+                    e0.record(stream)
+                    ctx.msm_g1_launch(db, nc, nb, 0)
+                    e1.record(stream)
+                    e1.synchronize()
+                    dt.append(e0.elapsed_time(e1))
+                dstats = ctx.msm_stats()
+                ctx.msm_g1_batch(hb, nc, nb)
+                t0 = time.perf_counter()
+                d_xy, d_inf = ctx.msm_g1_batch(hb, nc, nb)
+                d_e2e = (time.perf_counter() - t0) * 1e3
+                assert d_xy == out_xy and list(d_inf) == list(out_inf), "direct-lookup table: commitments differ from the bucket pipeline's"
+                ctx.prove_batch(hb, nc, roots, 1)
+                t0 = time.perf_counter()
+                ctx.prove_batch(hb, nc, roots, 1)
+                d_prove = (time.perf_counter() - t0) * 1e3
+                ctx.msm_g1(one, nc)
+                d_single = min(_timed(lambda: ctx.msm_g1(one, nc)) for _ in range(7))
+                ctx.set_option("direct_table_gb", 0)
+            commit["direct"] = {"table_gib_budget": args.direct_table_gb, "window_bits": dstats["window_bits"] if dstats else None,
+                                "table_build_ms": t_build, "ms_resident": allmax(min(dt[1:])), "ms_e2e": allmax(d_e2e),
+                                "ms_prove_e2e": allmax(d_prove), "ms_one_commit_e2e": d_single, "ms_one_commit_e2e_buckets": b_single}
         del db
 
     # ---------------- secondary kernels (rank 0, N = 1 only): G2 MSM, quotient / proof at k = 4096, trusted setup
@@ -533,6 +579,12 @@ def run_b200(args):
                               "ms_prove_e2e": commit["ms_prove_e2e"], "parity_asserted": True,
                               "parity_check": "sum of all commitments == [sum_b P_b(s)] G1 (checksum of checksums)",
                               "phases_ms": commit["phases"],
+                              "direct_table": None if "direct" not in commit else dict(
+                                  commit["direct"], commits_per_s=nbt / (commit["direct"]["ms_resident"] * 1e-3),
+                                  commits_per_s_e2e=nbt / (commit["direct"]["ms_e2e"] * 1e-3),
+                                  proofs_per_s_e2e=nbt / (commit["direct"]["ms_prove_e2e"] * 1e-3), bytes_identical_to_bucket_pipeline=True,
+                                  note="opt-in (kzg_gpu_set_option direct_table_gb): every multiple d*2^(cw)*G_i tabulated in HBM; no sort, "
+                                       "no buckets, no weighted reduction"),
                               "roofline": {"bound": "int32-imad", "peak": peak / 1e12, "unit": "TIMAD/s",
                                            "executed": {"imad_per_gpu": exec_imad, "achieved": exec_imad / (cms * 1e-3) / 1e12,
                                                         "frac": exec_imad / (cms * 1e-3) / peak,
@@ -697,6 +749,8 @@ def main():
     ap.add_argument("--no-strong", action="store_true")
     ap.add_argument("--strong-log2n", default="20,22", help="sizes of the single MSMs split N ways (strong scaling)")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--direct-table-gb", type=int, default=40,
+                    help="GiB of HBM the direct-lookup table of the 4097-point commit SRS may take (0: skip that measurement)")
     ap.add_argument("--single-process", action="store_true",
                     help="drive --gpus N devices from ONE process through the kzg_gpu_group C ABI (no torchrun, no NCCL)")
     args = ap.parse_args()

@@ -75,6 +75,9 @@ void kzg_gpu_ctx_destroy(kzg_gpu_ctx* ctx);
  * kzg_gpu_msm_partial_device — the point-range split folds and normalises once, after the exchange).
  * "tail" (1: the sort and the narrow end of the reduction run in two persistent cooperative kernels), "tail_proj" (1: that
  * end uses complete projective formulas on 8-lane teams for G1; 2: also for G2, on whole-warp teams), "table_pad" (experiment: 128-byte window-table entries),
+ * "direct_table_gb" (0 = off: GiB of device memory a DIRECT-LOOKUP table of the next SRS may take — every multiple
+ * d 2^(cw) G_i a digit can select, csrc/msm_direct.cuh; 4097 points: 32 GiB at c = 13, 61 at 14, 110 at 15 — G1 MSMs then
+ * skip sort, buckets and weighted reduction: for services that commit 4096-element blobs against one small SRS),
  * "table_ladder" (1: a large SRS also gets window tables of its first 8192 and 131072 points with window widths that suit
  * those sizes, used by MSMs that fit — a small commitment does not walk the bucket reduction of the big table),
  * "barrier_sleep" (ns between polls of the grid barrier).

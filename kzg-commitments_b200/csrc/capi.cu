@@ -89,6 +89,7 @@ int kzg_gpu_set_option(kzg_gpu_ctx* ctx, const char* name, long long value) {
   else if (n == "tail") { ok = value >= 0 && value <= 1; if (ok) ctx->opt_tail = (int)value; }
   else if (n == "barrier_sleep") { ok = value >= 0 && value <= 100000; if (ok) ctx->opt_barrier_sleep = (int)value; }
   else if (n == "tail_proj") { ok = value >= 0 && value <= 2; if (ok) ctx->opt_tail_proj = (int)value; }
+  else if (n == "direct_table_gb") { ok = value >= 0 && value <= 1024; if (ok) ctx->opt_direct_table_gb = (int)value; }
   else if (n == "table_ladder") { ok = value >= 0 && value <= 1; if (ok) ctx->opt_table_ladder = (int)value; }
   else if (n == "table_pad") { ok = value >= 0 && value <= 1; if (ok) ctx->opt_table_pad = (int)value; }
   else if (n == "team") { ok = value >= 0 && value <= 1; if (ok) ctx->opt_team = (int)value; }

@@ -22,6 +22,7 @@
 #include "diag.cuh"
 #include "msm.cuh"
 #include "msm_affine.cuh"
+#include "msm_direct.cuh"
 #include "msm_team.cuh"
 #include "msm_tail.cuh"
 #include "msm_tail_proj.cuh"
@@ -74,7 +75,7 @@ struct kzg_gpu_ctx {
   std::recursive_mutex mu;  // the reference API is re-entrant for readers; serialise use of the shared scratch
   // options
   int opt_window_bits = 0, opt_precompute = 2, opt_task_chunk = 0, opt_reduce_chunk = 0, opt_setup_g2 = 1,
-      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1, opt_table_pad = 0, opt_barrier_sleep = 64, opt_tail_proj = 1, opt_table_ladder = 1;
+      opt_profile = 0, opt_affine_levels = -1, opt_team = 1, opt_long_division = 3, opt_finish_affine = 1, opt_tail = 1, opt_table_pad = 0, opt_barrier_sleep = 64, opt_tail_proj = 1, opt_table_ladder = 1, opt_direct_table_gb = 0;
   cudaEvent_t phase_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 
   virtual ~kzg_gpu_ctx() {}
@@ -172,6 +173,10 @@ struct Ctx final : kzg_gpu_ctx {
   static constexpr int N_RUNGS = 2;
   static constexpr uint64_t RUNG_POINTS[N_RUNGS] = {8192, 131072};
   TableRung rungs[N_RUNGS];
+  // Direct-lookup table (msm_direct.cuh): D[w][i][d-1] = d 2^(c w) G_i for every digit value, for a SMALL SRS when the
+  // caller grants the memory ("direct_table_gb").  G1 MSMs then need no sort, no buckets and no weighted reduction.
+  DevBuf g1_direct;
+  int direct_c = 0, direct_W = 0;
   // fixed-base tables of the generators
   // (constants of the curve: built once per process and device, shared by every context, never freed)
   struct FbShared { Affine<Fp>* t1 = nullptr; Affine<Fp2>* t2 = nullptr; };
@@ -257,6 +262,8 @@ struct Ctx final : kzg_gpu_ctx {
     g1_table.release();
     g2_table.release();
     for (TableRung& rg : rungs) { rg.buf.release(); rg.n = 0; }
+    g1_direct.release();
+    direct_c = direct_W = 0;
     table_c = table_W = 0;
     if (srs_n == 0) return KZG_GPU_OK;
     if (!opt_precompute) return reserve_scratch();
@@ -293,6 +300,36 @@ struct Ctx final : kzg_gpu_ctx {
             nk, nk, ck, Wk, g1.as<Affine<Fp>>(), rg.buf.template as<Affine<Fp>>(), sizeof(Affine<Fp>));
       LAUNCHED();
       rg.n = nk; rg.c = ck; rg.W = Wk;
+    }
+    if (opt_direct_table_gb > 0 && !opt_window_bits) {
+      // the widest window (fewest additions per scalar) whose table fits the memory the caller granted
+      const double budget = (double)opt_direct_table_gb * 1073741824.0;
+      int cd = 0, Wd = 0;
+      for (int cc = 16; cc >= 8; cc--) {
+        const int Wc = (C::SCALAR_BITS + 1 + cc - 1) / cc;
+        if (Wc > MAXW) continue;
+        if ((double)Wc * (double)srs_n * (double)(1ull << (cc - 1)) * sizeof(Affine<Fp>) <= budget) { cd = cc; Wd = Wc; break; }
+      }
+      if (cd) {
+        const uint64_t H = 1ull << (cd - 1), rows = (uint64_t)Wd * srs_n;
+        CK(g1_direct.ensure((size_t)rows * H * sizeof(Affine<Fp>)));
+        // entry d = 1 of every row: 2^(cd w) G_i, written by the window-table kernel with one row of H entries as its stride
+        if (srs_n <= TABLE_TEAM_MAX_POINTS)
+          msm_precompute_table_team<Fp, MAXW><<<(unsigned)((TeamWidth<Fp>::LANES * srs_n + 127) / 128), 128, 0, stream>>>(
+              srs_n, srs_n, cd, Wd, g1.as<Affine<Fp>>(), g1_direct.as<Affine<Fp>>(), (size_t)H * sizeof(Affine<Fp>));
+        else
+          msm_precompute_table<Fp, MAXW><<<(unsigned)((srs_n + 127) / 128), 128, 0, stream>>>(
+              srs_n, srs_n, cd, Wd, g1.as<Affine<Fp>>(), g1_direct.as<Affine<Fp>>(), (size_t)H * sizeof(Affine<Fp>));
+        LAUNCHED();
+        for (int level = 0; level + 1 < cd; level++) {
+          const uint64_t total = rows << level;
+          direct_table_fill<Fp><<<(unsigned)std::min<uint64_t>((total + 127) / 128, (uint64_t)148 * 256), 128, 0, stream>>>(
+              level, rows, H, g1_direct.as<Affine<Fp>>());
+          LAUNCHED();
+        }
+        direct_c = cd;
+        direct_W = Wd;
+      }
     }
     CK(cudaStreamSynchronize(stream));
     table_c = c;
@@ -803,6 +840,109 @@ struct Ctx final : kzg_gpu_ctx {
     return KZG_GPU_OK;
   }
 
+  // shape of a direct-lookup pass: ~2^18 threads when there is enough work, between 4 and 8 W additions per thread
+  DirectShape direct_shape(uint64_t count, uint64_t batch, uint64_t base_offset) const {
+    DirectShape sh{};
+    sh.c = direct_c; sh.W = direct_W; sh.H = 1ull << (direct_c - 1); sh.n_table = srs_n;
+    sh.n = count; sh.batch = batch; sh.base_offset = base_offset;
+    const uint64_t adds = count * batch * (uint64_t)direct_W;
+    const uint64_t per_thread = std::min<uint64_t>(8ull * direct_W, std::max<uint64_t>(4, adds >> 18));
+    uint64_t spt = 1;
+    if (per_thread >= (uint64_t)direct_W) { sh.wpt = direct_W; spt = per_thread / direct_W; }
+    else sh.wpt = (int)per_thread;
+    sh.groups = (direct_W + sh.wpt - 1) / sh.wpt;
+    sh.spt = (int)spt;
+    uint64_t Q = (count + spt - 1) / spt;
+    if (sh.groups > 1) Q = (Q + 31) / 32 * 32;  // a warp stays inside one window group (direct_accumulate)
+    sh.P = Q * (uint64_t)sh.groups;
+    sh.P2 = 1;
+    while (sh.P2 < sh.P) sh.P2 <<= 1;
+    return sh;
+  }
+  // One direct-lookup pass for `batch` G1 MSMs of `count` scalars (device-resident bytes): accumulate, pairwise trees,
+  // normalisation.  Same outputs as enqueue_msm.
+  int enqueue_msm_direct(const uint8_t* d_scalars, uint64_t count, uint64_t batch, uint64_t base_offset) {
+    using F = Fp;
+    const DirectShape sh = direct_shape(count, batch, base_offset);
+    const uint64_t slots = batch * sh.P2;
+    CK(partial.ensure(slots * sizeof(XYZZ<F>)));
+    CK(red0.ensure(std::max<uint64_t>(1, slots / 2) * sizeof(XYZZ<F>)));
+    CK(red2.ensure(batch * sizeof(XYZZ<F>)));
+    CK(red3.ensure(batch * sizeof(XYZZ<F>)));
+    CK(group_out.ensure(batch * sizeof(XYZZ<F>)));
+    CK(out_bytes.ensure(batch * (size_t)(4 * M)));
+    CK(out_inf.ensure(batch * sizeof(int)));
+    CK(out_xyzz.ensure(batch * sizeof(XYZZ<F>)));
+    const bool use_tail = opt_tail && opt_team;
+    if (use_tail) {
+      int rct = prepare_tail<F>();
+      if (rct) return rct;
+    }
+    for (int sl = 0; sl < chunk_slices; sl++) CK(cudaStreamWaitEvent(stream, chunk_ev[sl], 0));  // scalars still arriving in chunks
+    chunk_slices = 0;
+    phase_mark(0);
+    phase_mark(1);
+    direct_accumulate<C, F><<<(unsigned)std::min<uint64_t>((slots + 127) / 128, (uint64_t)1 << 30), 128, 0, stream>>>(
+        sh, d_scalars, g1_direct.as<Affine<F>>(), partial.as<XYZZ<F>>());
+    LAUNCHED();
+    phase_mark(2);
+    XYZZ<F>*in = partial.as<XYZZ<F>>(), *out = red0.as<XYZZ<F>>();
+    uint64_t len = sh.P2;
+    const bool finish_in_tail = use_tail && batch <= tail_threads_total() / 32;
+    const uint64_t tail_cap = finish_in_tail ? 4 * tail_threads_total() : 0;
+    while (len > 1 && batch * (len / 2) > tail_cap) {  // wide levels: launches of their own
+      PairJob<F> j0{in, out, batch * (len / 2)}, j1{in, out, 0};
+      if (opt_team && j0.n_out <= TEAM_MAX_ITEMS) {
+        dim3 grid((unsigned)((WIDE_LANES * j0.n_out + 127) / 128), 1);
+        msm_pair_sum_team<F><<<grid, 128, 0, stream>>>(j0, j1);
+      } else {
+        dim3 grid((unsigned)std::min<uint64_t>((j0.n_out + 127) / 128, (uint64_t)148 * 64), 1);
+        msm_pair_sum<F><<<grid, 128, 0, stream>>>(j0, j1);
+      }
+      LAUNCHED();
+      std::swap(in, out);
+      len /= 2;
+    }
+    phase_mark(3);
+    if (finish_in_tail) {
+      // the rest in the cooperative tail kernel, entered at its second tree stage: "row sums" = our partial sums (len per
+      // MSM), "column sums" = one point at infinity per MSM, no doublings in between (h = 0), then normalisation and bytes
+      CK(cudaMemsetAsync(red2.p, 0, batch * sizeof(XYZZ<F>), stream));
+      TailArgs<F> ta{};
+      ta.first_stage = TAIL_TREES2; ta.last_stage = TAIL_FINISH;
+      ta.barrier = barrier_buf.as<GridBarrier>();
+      ta.rin = in; ta.rout = out; ta.cin = red2.as<XYZZ<F>>(); ta.cout = red3.as<XYZZ<F>>();
+      ta.groups = batch; ta.R = 1; ta.Cn = 1; ta.r_len = len; ta.c_len = 1; ta.h = 0;
+      ta.group_out = group_out.as<XYZZ<F>>();
+      ta.batch = batch; ta.groups_per_msm = 1; ta.c = sh.c; ta.modbytes = M; ta.want_affine = opt_finish_affine;
+      ta.out_bytes = out_bytes.as<uint8_t>(); ta.is_inf = out_inf.as<int>(); ta.out_xyzz = out_xyzz.as<XYZZ<F>>();
+      int rc;
+      if (opt_tail_proj) {
+        B3 b3{3 * C::G1_B, 0};
+        rc = launch_cooperative((const void*)msm_tail_proj<Fp>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES, &b3);
+      } else {
+        rc = launch_cooperative((const void*)msm_tail<Fp>, 1u << 20, TAIL_THREADS, &ta, TAIL_SMEM_BYTES);
+      }
+      if (rc) return rc;
+    } else {
+      // (large batches) `in` holds one sum per MSM
+      if (opt_team && batch <= TEAM_MAX_ITEMS)
+        msm_finish_team<F><<<(unsigned)((TeamWidth<F>::LANES * batch + 127) / 128), 128, 0, stream>>>(
+            batch, 1, sh.c, in, out_bytes.as<uint8_t>(), out_inf.as<int>(), M, out_xyzz.as<XYZZ<F>>(), opt_finish_affine);
+      else {
+        const int lane_stride = batch <= 65536 ? 32 : 1;
+        msm_finish<F><<<(unsigned)((batch * lane_stride + 127) / 128), 128, 0, stream>>>(
+            batch, 1, sh.c, in, out_bytes.as<uint8_t>(), out_inf.as<int>(), M, out_xyzz.as<XYZZ<F>>(), opt_finish_affine, lane_stride);
+      }
+      LAUNCHED();
+    }
+    phase_mark(4);
+    last_batch = batch;
+    last_records = count * batch * (uint64_t)sh.W; last_nbuckets = 0; last_c = sh.c; last_chunk = sh.wpt;
+    last_direct_partials = batch * sh.P;
+    return KZG_GPU_OK;
+  }
+
   // largest number of MSMs of `count` scalars that one pass may take
   uint64_t max_batch_per_pass(uint64_t count, int W) const {
     const uint64_t rec_budget = 1ull << 27;  // records per pass (digits + sorted = 1 GiB)
@@ -840,6 +980,9 @@ struct Ctx final : kzg_gpu_ctx {
         if (rg.n && base_offset + count <= rg.n) { rung = &rg; break; }
     const int Wguess = rung ? rung->W : use_table ? table_W : (C::SCALAR_BITS + 8) / 8;
     uint64_t per_pass = do_fetch ? max_batch_per_pass(count, Wguess) : batch;
+    const bool direct = group == 1 && g1_direct.p != nullptr && opt_direct_table_gb > 0;
+    if (direct && do_fetch)  // partial sums of a pass: at most 2 GiB
+      per_pass = std::max<uint64_t>(1, std::min<uint64_t>(batch, (1ull << 31) / (direct_shape(count, batch, base_offset).P2 * sizeof(XYZZ<Fp>))));
     // Host scalars of a large batch: split into passes of >= 128 MSMs so that the copy of pass i + 1 (copy stream,
     // second staging buffer) runs under the kernels of pass i; one pass would leave the whole H2D exposed
     // (134 MB = 2.4 ms for 1024 blobs of 4096 coefficients in front of 35 ms of compute).
@@ -902,7 +1045,9 @@ struct Ctx final : kzg_gpu_ctx {
         d_scal = scal.as<uint8_t>();
       }
       int rc;
-      if (group == 1)
+      if (direct)
+        rc = enqueue_msm_direct(d_scal, count, nb, base_offset);
+      else if (group == 1)
         rc = rung ? enqueue_msm<Fp>(g1.as<Affine<Fp>>(), rung->buf.template as<Affine<Fp>>(), rung->c, d_scal, count, nb, base_offset, false, rung->n)
                   : enqueue_msm<Fp>(g1.as<Affine<Fp>>(), use_table ? g1_table.as<Affine<Fp>>() : nullptr, table_c, d_scal,
                                     count, nb, base_offset);
@@ -1449,10 +1594,15 @@ struct Ctx final : kzg_gpu_ctx {
   // shape of the most recent MSM pass: records, buckets, tasks, most tasks in one bucket, window bits, task chunk
   uint64_t last_records = 0, last_nbuckets = 0;
   int last_c = 0, last_chunk = 0;
+  uint64_t last_direct_partials = 0;
   int msm_stats(uint64_t* out, int n) override {
     std::lock_guard<std::recursive_mutex> lock(mu);
     CK(cudaSetDevice(device));
     if (!out || n < 6) return KZG_GPU_ERR_ARG;
+    if (!last_nbuckets && last_records && last_c) {  // a direct-lookup pass: no buckets; "tasks" = partial sums, chunk = windows per thread
+      out[0] = last_records; out[1] = 0; out[2] = last_direct_partials; out[3] = 0; out[4] = (uint64_t)last_c; out[5] = (uint64_t)last_chunk;
+      return KZG_GPU_OK;
+    }
     if (!last_nbuckets) return KZG_GPU_ERR_STATE;
     uint32_t ntasks = 0, max_nt = 0;
     CK(cudaMemcpyAsync(&ntasks, task_first.as<uint32_t>() + last_nbuckets, 4, cudaMemcpyDeviceToHost, stream));

@@ -147,6 +147,48 @@ def test_table_ladder_gives_the_same_bytes(cname):
     ctx.close()
 
 
+@pytest.mark.parametrize("cname", CURVE_NAMES)
+def test_direct_lookup_table_gives_the_same_bytes(cname):
+    """"direct_table_gb": every multiple a digit can select is tabulated (csrc/msm_direct.cuh); G1 MSMs become plain sums of
+    looked-up points.  Same bytes as the bucket pipeline and as the oracle: single MSMs, batches that finish inside the tail
+    kernel and larger ones, point ranges, edge scalars, a degenerate SRS (secret 1: every point equal; secret 0: infinities)."""
+    C = get_curve(cname)
+    rng = random.Random(321 + C.id)
+    nb2 = None
+    for secret, n in ((rng.randrange(2, C.r), 300), (1, 40), (0, 40)):
+        ctx = kzg_b200.Context(cname, 0)
+        ctx.set_option("setup_g2", 0)
+        ctx.set_option("direct_table_gb", 1)     # 300 points: c = 11 or 12 fits 1 GiB
+        ctx.setup_powers(secret, n, want_bytes=False)
+        nb2 = 2 * ctx.M
+        cases = [(1, 1, 0), (2, 1, 0), (n, 1, 0), (n - 3, 1, 3), (n, 7, 0), (17, 700, 0), (n, 40, 0)]
+        for count, batch, off in cases:
+            coeffs = [rng.randrange(C.r) for _ in range(count * batch)]
+            if batch == 7:
+                coeffs[:count] = [0] * count                      # an all-zero polynomial inside a batch
+                coeffs[count:2 * count] = [C.r - 1] * count
+                coeffs[2 * count] = 1
+            raw = C.scalars_to_bytes(coeffs)
+            call = (lambda: ctx.msm_g1_batch(raw, count, batch)) if batch > 1 else (lambda: ctx.msm_g1(raw, count, off))
+            ctx.set_option("direct_table_gb", 1)
+            got = call()
+            ctx.set_option("direct_table_gb", 0)                  # the table stays; the bucket pipeline runs
+            assert call() == got, (secret, count, batch, off)
+            if batch <= 7:
+                for b in range(batch):
+                    want = C.mul(C.poly_eval(coeffs[b * count:(b + 1) * count], secret) * pow(secret, off, C.r) % C.r, C.g1)
+                    xy = got[0][b * nb2:(b + 1) * nb2]
+                    inf = got[1][b] if batch > 1 else got[1]
+                    assert (xy, inf) == (C.g1_to_octet(want)[1:], want is None), (secret, count, batch, off, b)
+        # the sum is the point at infinity: c0 + c1 s = 0
+        if secret > 1:
+            ctx.set_option("direct_table_gb", 1)
+            sc = [(C.r - 9 * secret % C.r) % C.r, 9]
+            xy, inf = ctx.msm_g1(C.scalars_to_bytes(sc), 2)
+            assert inf and xy == bytes(len(xy))
+        ctx.close()
+
+
 def test_tail_at_2_16_and_2_18():
     """sizes where part of the reduction is still wide launches and the rest runs in the tail kernel"""
     C = get_curve("bls12381")
