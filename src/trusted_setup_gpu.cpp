@@ -290,6 +290,11 @@ SidePtr new_side(size_t n) {
   int rc = ndev > 0 ? kzg_gpu_group_create(&side->group, CURVE_ID, nullptr, ndev) : KZG_GPU_ERR_CUDA;
   if (rc) fail(nullptr, rc, "kzg_gpu_group_create (a CUDA device is required; there is no CPU fallback)");
   side->n = n;
+  // KZG_GPU_DIRECT_TABLE_GB=<GiB>: a small setup (the 4096-element blobs of src/blob.cpp) may also keep the direct-lookup
+  // table of csrc/msm_direct.cuh — 32 GiB for 4097 points on BLS12-381 — which takes a degree-4096 create_commit from
+  // 0.49 to 0.31 ms.  Off unless asked for: the table is per resident setup.
+  if (const char* e = getenv("KZG_GPU_DIRECT_TABLE_GB"))
+    if (atoi(e) > 0 && n <= 16384) kzg_gpu_group_set_option(side->group, "direct_table_gb", atoi(e));
   return side;
 }
 void remember_locked(const void* self, const SidePtr& side, const Digest& digest, std::vector<uint8_t> stamp) {
