@@ -46,6 +46,15 @@ struct DevBuf {
     if (e == cudaSuccess) cap = want;
     return e;
   }
+  cudaError_t ensure_exact(size_t bytes) {  // no head-room: tables of tens of GB
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
   void release() {
     if (p) cudaFree(p);
     p = nullptr;
@@ -310,9 +319,13 @@ struct Ctx final : kzg_gpu_ctx {
         if (Wc > MAXW) continue;
         if ((double)Wc * (double)srs_n * (double)(1ull << (cc - 1)) * sizeof(Affine<Fp>) <= budget) { cd = cc; Wd = Wc; break; }
       }
+      if (cd) {  // the grant is an upper bound, not a promise: with the memory taken (other resident setups) the SRS simply has no such table
+        const cudaError_t ed = g1_direct.ensure_exact((size_t)Wd * srs_n * (1ull << (cd - 1)) * sizeof(Affine<Fp>));
+        if (ed == cudaErrorMemoryAllocation) { cudaGetLastError(); cd = 0; }
+        else if (ed != cudaSuccess) return cuda_fail(ed, "g1_direct.ensure");
+      }
       if (cd) {
         const uint64_t H = 1ull << (cd - 1), rows = (uint64_t)Wd * srs_n;
-        CK(g1_direct.ensure((size_t)rows * H * sizeof(Affine<Fp>)));
         // entry d = 1 of every row: 2^(cd w) G_i, written by the window-table kernel with one row of H entries as its stride
         if (srs_n <= TABLE_TEAM_MAX_POINTS)
           msm_precompute_table_team<Fp, MAXW><<<(unsigned)((TeamWidth<Fp>::LANES * srs_n + 127) / 128), 128, 0, stream>>>(
@@ -392,6 +405,13 @@ struct Ctx final : kzg_gpu_ctx {
     if (have_g2 && srs_n <= (1ull << 16))  // verify-side MSMs (k + 1 terms)
       rc = enqueue_msm<Fp2>(g2.as<Affine<Fp2>>(), table_c ? g2.as<Affine<Fp2>>() : nullptr, table_c, nullptr, cnt, 1, 0, true);
     if (rc) return rc;
+    if (g1_direct.p) {  // the partial-sum slots of one direct-lookup MSM over the whole SRS (msm_direct.cuh)
+      const DirectShape ds = direct_shape(cnt, 1, 0);
+      CK(partial.ensure(ds.P2 * sizeof(XYZZ<Fp>)));
+      CK(red0.ensure(std::max<uint64_t>(1, ds.P2 / 2) * sizeof(XYZZ<Fp>)));
+      CK(red2.ensure(sizeof(XYZZ<Fp>)));
+      CK(red3.ensure(sizeof(XYZZ<Fp>)));
+    }
     return warm_up();
   }
   // One two-term MSM of zero scalars per group right after the SRS became resident: the first launch of every kernel of
