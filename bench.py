@@ -21,6 +21,8 @@ points per GPU (BASELINE.json config "G1 MSM 2^16-2^22 synthetic SRS", the size 
              ways by contiguous point range, and 4096 blob commitments IN TOTAL sharded N ways (512 per GPU at N = 8),
              each with its own parity assertion.
   commit     batched blob commitments + single-point proofs (config 3) with roofline and CPU baseline objects.
+             commit.direct_table: the same batch (and one single commitment) through the opt-in direct-lookup table
+             (csrc/msm_direct.cuh, --direct-table-gb G, default 40 GiB of HBM; 0 skips it), outputs asserted byte-identical.
   secondary  the other kernels of the path: G2 MSM of 4097 terms (BN254, BLS12-381), quotient and proof at
              n = 8192 / k = 4096 (config 5), trusted setup of 2^20 indices.
 Reference arm (--impl reference): the UNMODIFIED reference library (oracle/_ref/kzgref-bls12381, built from
