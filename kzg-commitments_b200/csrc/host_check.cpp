@@ -12,6 +12,7 @@
 #include "diag.cuh"
 #include "msm.cuh"
 #include "msm_affine.cuh"
+#include "msm_direct.cuh"
 
 using namespace kzgb200;
 
@@ -152,6 +153,56 @@ int msm_host(uint64_t srs_n, const uint8_t* pts_bytes, const uint8_t* scalars, u
   return 0;
 }
 
+// The direct-lookup path of ctx.cuh::enqueue_msm_direct (msm_direct.cuh) with loops in place of launches: the table of
+// every digit multiple, one partial sum per (scalars, window group) slot, pairwise trees, normalisation.  G1 only.
+template <class C>
+int msm_direct_host(uint64_t srs_n, const uint8_t* pts_bytes, const uint8_t* scalars, uint64_t count, uint64_t batch,
+                    uint64_t base_offset, int c, int wpt, int spt, uint8_t* out, int* is_inf) {
+  using F = Field<typename C::FpP>;
+  const int M = C::MODBYTES;
+  std::vector<Affine<F>> bases(srs_n);
+  for (uint64_t i = 0; i < srs_n; i++) affine_from_bytes(bases[i], pts_bytes + i * (uint64_t)(2 * M), M);
+  DirectShape sh{};
+  sh.c = c;
+  sh.W = (C::SCALAR_BITS + 1 + c - 1) / c;
+  sh.H = 1ull << (c - 1);
+  sh.n_table = srs_n;
+  sh.n = count;
+  sh.batch = batch;
+  sh.base_offset = base_offset;
+  sh.wpt = wpt;
+  sh.groups = (sh.W + wpt - 1) / wpt;
+  sh.spt = sh.groups > 1 ? 1 : spt;
+  uint64_t Q = (count + sh.spt - 1) / sh.spt;
+  if (sh.groups > 1) Q = (Q + 31) / 32 * 32;
+  sh.P = Q * (uint64_t)sh.groups;
+  sh.P2 = 1;
+  while (sh.P2 < sh.P) sh.P2 <<= 1;
+  // D[w][i][0] = 2^(c w) G_i (device: msm_precompute_table with a row of H entries as its stride), then the fill levels
+  const uint64_t rows = (uint64_t)sh.W * srs_n;
+  std::vector<Affine<F>> direct(rows * sh.H);
+  for (uint64_t i = 0; i < srs_n; i++) {
+    XYZZ<F> cur = XYZZ<F>::from_affine(bases[i]);
+    direct[i * sh.H] = bases[i];
+    for (int w = 1; w < sh.W; w++) {
+      for (int k = 0; k < c; k++) cur.dbl();
+      direct[((uint64_t)w * srs_n + i) * sh.H] = cur.is_inf() ? Affine<F>::inf() : cur.to_affine();
+    }
+  }
+  for (int level = 0; level + 1 < c; level++)
+    for (uint64_t t = 0; t < (rows << level); t++) direct_fill_thread<F>(level, sh.H, direct.data(), t);
+  std::vector<XYZZ<F>> in(batch * sh.P2);
+  for (uint64_t t = 0; t < batch * sh.P2; t++) direct_accumulate_thread<C, F>(sh, scalars, direct.data(), in.data(), t);
+  for (uint64_t len = sh.P2; len > 1; len /= 2) {
+    std::vector<XYZZ<F>> nxt(batch * (len / 2));
+    PairJob<F> jb{in.data(), nxt.data(), batch * (len / 2)};
+    for (uint64_t i = 0; i < jb.n_out; i++) msm_pair_sum_thread<F>(jb, i);
+    in.swap(nxt);
+  }
+  for (uint64_t m = 0; m < batch; m++) msm_finish_thread<F>(1, c, in.data(), out, is_inf, M, (XYZZ<F>*)nullptr, m);
+  return 0;
+}
+
 template <class C>
 int dispatch_field(int which, int op, const uint32_t* a, const uint32_t* b, uint32_t* out) {
   return which == 0 ? field_op<Field<typename C::FpP>>(op, a, b, out) : field_op<Field<typename C::FrP>>(op, a, b, out);
@@ -202,6 +253,18 @@ int hc_msm(int curve, int group, uint64_t srs_n, const uint8_t* pts, const uint8
     case 0: return dispatch_msm<Curve_BN158>(group, srs_n, pts, scalars, count, batch, base_offset, c, chunk, bpc, precomp, out, is_inf);
     case 1: return dispatch_msm<Curve_BN254>(group, srs_n, pts, scalars, count, batch, base_offset, c, chunk, bpc, precomp, out, is_inf);
     case 2: return dispatch_msm<Curve_BLS12381>(group, srs_n, pts, scalars, count, batch, base_offset, c, chunk, bpc, precomp, out, is_inf);
+  }
+  return -1;
+}
+
+// G1 MSM through the direct-lookup table; wpt: windows per slot; spt: scalars per slot (used when wpt covers all windows)
+int hc_msm_direct(int curve, uint64_t srs_n, const uint8_t* pts, const uint8_t* scalars, uint64_t count, uint64_t batch,
+                  uint64_t base_offset, int c, int wpt, int spt, uint8_t* out, int* is_inf) {
+  if (c < 2 || c > 12 || wpt < 1 || spt < 1) return -1;
+  switch (curve) {
+    case 0: return msm_direct_host<Curve_BN158>(srs_n, pts, scalars, count, batch, base_offset, c, wpt, spt, out, is_inf);
+    case 1: return msm_direct_host<Curve_BN254>(srs_n, pts, scalars, count, batch, base_offset, c, wpt, spt, out, is_inf);
+    case 2: return msm_direct_host<Curve_BLS12381>(srs_n, pts, scalars, count, batch, base_offset, c, wpt, spt, out, is_inf);
   }
   return -1;
 }

@@ -37,60 +37,72 @@ struct DirectShape {
   uint64_t P2;           // slots per MSM (power of two >= P; the rest are written as infinity)
 };
 
+// The per-thread bodies are plain host/device functions (as in msm.cuh) so that csrc/host_check.cpp can run the same
+// code on the CPU through the carry-flag emulation; the __global__ wrappers only add the grid-stride loop.
+// entry (2^level + r) of a row, r = 1 .. 2^level (r = 2^level is the doubling: the mixed addition's P + P branch)
+template <class F>
+KZG_HD void direct_fill_thread(int level, uint64_t H, Affine<F>* direct, uint64_t t) {
+  const uint64_t per = 1ull << level;
+  const uint64_t row = t >> level, r = (t & (per - 1)) + 1;
+  Affine<F>* e = direct + row * H;
+  XYZZ<F> acc = XYZZ<F>::from_affine(e[per - 1]);
+  acc.madd(e[r - 1], false);
+  e[per + r - 1] = acc.is_inf() ? Affine<F>::inf() : acc.to_affine();
+}
+
+// one partial sum per slot: slot p of MSM b is (scalars q spt .. q spt + spt - 1, window group g), p = g * (P / groups) + q;
+// slots P .. P2-1 are infinity.  The digits are those of msm_digits_thread (signed, carry from the windows below).
+template <class C, class F>
+KZG_HD void direct_accumulate_thread(const DirectShape& sh, const uint8_t* scalars, const Affine<F>* direct, XYZZ<F>* partial,
+                                     uint64_t t) {
+  const uint64_t b = t / sh.P2, p = t - b * sh.P2;
+  XYZZ<F> acc = XYZZ<F>::inf();
+  if (p < sh.P) {
+    // group-major: the threads of a warp share the window group, so they reach their additions in the same loop
+    // iterations (scalar-major slots made a warp walk through all W windows one divergent subset at a time: 4x slower)
+    // (Q = P / groups is a multiple of 32 when there are several groups, so a warp never straddles two of them)
+    const uint64_t Q = sh.P / (uint64_t)sh.groups;
+    const int g = (int)(p / Q);
+    const uint64_t q = p - (uint64_t)g * Q;
+    const int w0 = g * sh.wpt, w1 = (w0 + sh.wpt < sh.W) ? w0 + sh.wpt : sh.W;
+    const uint32_t half = 1u << (sh.c - 1);
+    const uint64_t i_end = (q + 1) * (uint64_t)sh.spt;
+    const uint64_t i1 = i_end < sh.n ? i_end : sh.n;
+    for (uint64_t i = q * (uint64_t)sh.spt; i < i1; i++) {
+      uint32_t k[C::FrP::L];
+      load_scalar<C>(scalars, b * sh.n + i, k);
+      uint32_t carry = 0;
+      for (int w = 0; w < w1; w++) {
+        const uint32_t raw = scalar_bits<C::FrP::L>(k, w * sh.c, sh.c) + carry;
+        int32_t d;
+        if (raw > half) { d = (int32_t)raw - (int32_t)(1u << sh.c); carry = 1; }
+        else { d = (int32_t)raw; carry = 0; }
+        if (w >= w0 && d != 0) {
+          const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
+          const Affine<F> pt = direct[((uint64_t)w * sh.n_table + sh.base_offset + i) * sh.H + (mag - 1)];
+          acc.madd(pt, d < 0);
+        }
+      }
+    }
+  }
+  partial[t] = acc;
+}
+
 #if defined(__CUDACC__)
-// entry (2^level + r) of every row, r = 1 .. 2^level (r = 2^level is the doubling: the mixed addition's P + P branch)
 template <class F>
 __global__ void __launch_bounds__(128)
 direct_table_fill(int level, uint64_t rows, uint64_t H, Affine<F>* __restrict__ direct) {
-  const uint64_t per = 1ull << level, total = rows << level;
-  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x) {
-    const uint64_t row = t >> level, r = (t & (per - 1)) + 1;
-    Affine<F>* e = direct + row * H;
-    XYZZ<F> acc = XYZZ<F>::from_affine(e[per - 1]);
-    acc.madd(e[r - 1], false);
-    e[per + r - 1] = acc.is_inf() ? Affine<F>::inf() : acc.to_affine();
-  }
+  const uint64_t total = rows << level;
+  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x)
+    direct_fill_thread<F>(level, H, direct, t);
 }
-
-// one partial sum per thread: slot p of MSM b is (scalars q spt .. q spt + spt - 1, window group g), p = g * (P / groups) + q;
-// slots P .. P2-1 are infinity.  The digits are those of msm_digits_thread (signed, carry from the windows below).
 template <class C, class F>
 __global__ void __launch_bounds__(128)
 direct_accumulate(DirectShape sh, const uint8_t* __restrict__ scalars, const Affine<F>* __restrict__ direct,
                   XYZZ<F>* __restrict__ partial) {
   const uint64_t total = sh.batch * sh.P2;
-  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x) {
-    const uint64_t b = t / sh.P2, p = t - b * sh.P2;
-    XYZZ<F> acc = XYZZ<F>::inf();
-    if (p < sh.P) {
-      // group-major: the threads of a warp share the window group, so they reach their additions in the same loop
-      // iterations (scalar-major slots made a warp walk through all W windows one divergent subset at a time: 4x slower)
-      // (Q = P / groups is a multiple of 32 when there are several groups, so a warp never straddles two of them)
-      const uint64_t Q = sh.P / (uint64_t)sh.groups;
-      const int g = (int)(p / Q);
-      const uint64_t q = p - (uint64_t)g * Q;
-      const int w0 = g * sh.wpt, w1 = min(sh.W, w0 + sh.wpt);
-      const uint32_t half = 1u << (sh.c - 1);
-      const uint64_t i1 = min(sh.n, (q + 1) * (uint64_t)sh.spt);
-      for (uint64_t i = q * (uint64_t)sh.spt; i < i1; i++) {
-        uint32_t k[C::FrP::L];
-        load_scalar<C>(scalars, b * sh.n + i, k);
-        uint32_t carry = 0;
-        for (int w = 0; w < w1; w++) {
-          const uint32_t raw = scalar_bits<C::FrP::L>(k, w * sh.c, sh.c) + carry;
-          int32_t d;
-          if (raw > half) { d = (int32_t)raw - (int32_t)(1u << sh.c); carry = 1; }
-          else { d = (int32_t)raw; carry = 0; }
-          if (w >= w0 && d != 0) {
-            const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
-            const Affine<F> pt = direct[((uint64_t)w * sh.n_table + sh.base_offset + i) * sh.H + (mag - 1)];
-            acc.madd(pt, d < 0);
-          }
-        }
-      }
-    }
-    partial[t] = acc;
-  }
+  for (uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x)
+    direct_accumulate_thread<C, F>(sh, scalars, direct, partial, t);
 }
 #endif
 

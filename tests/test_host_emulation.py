@@ -25,6 +25,9 @@ def hc():
                            ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, ctypes.c_int,
                            ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int)]
     lib.hc_selftest.argtypes = [ctypes.c_int, ctypes.c_uint32]
+    lib.hc_msm_direct.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_uint64,
+                                  ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_char_p,
+                                  ctypes.POINTER(ctypes.c_int)]
     return lib
 
 
@@ -136,3 +139,36 @@ def test_msm_pipeline_edges(hc, cname):
         assert raw[b * 2 * C.M:(b + 1) * 2 * C.M] == C.g1_to_octet(want)[1:]
     raw, inf = _run(hc, C, 1, g1, C.scalars_to_bytes(sc[:9]), 9, base_offset=11, c=5, precomp=1)
     assert raw == C.g1_to_octet(C.msm(sc[:9], g1[11:20]))[1:]
+
+
+@pytest.mark.parametrize("cname", ["bls12381", "bn254"])
+def test_direct_lookup_path(hc, cname):
+    """csrc/msm_direct.cuh on the host: the table of every digit multiple, one partial sum per (scalars, window group)
+    slot (group-major, padded to warps), pairwise trees — against the oracle's MSM; repeated and opposite bases, an
+    infinity in the SRS, point ranges, batches, non-canonical scalars."""
+    C = get_curve(cname)
+    rng = random.Random(2024 + C.id)
+    P = C.mul(11, C.g1)
+    pts = [C.g1, P, P, C.neg(P), None, C.mul(rng.randrange(C.r), C.g1), C.mul(7, C.g1)]
+    raw_pts = _pts_bytes(C, pts, False)
+
+    def run(scalars, count, batch=1, off=0, c=3, wpt=4, spt=1):
+        raw_sc = b"".join((s % (1 << (8 * C.SB))).to_bytes(C.SB, "little") for s in scalars)
+        out = ctypes.create_string_buffer(batch * 2 * C.M)
+        inf = (ctypes.c_int * batch)()
+        assert hc.hc_msm_direct(C.id, len(pts), raw_pts, raw_sc, count, batch, off, c, wpt, spt, out, inf) == 0
+        return out.raw, list(inf)
+
+    n = len(pts)
+    for sc in ([rng.randrange(C.r) for _ in range(n)], [1] * n, [C.r - 1] * n, [0] * n,
+               [5, 3, C.r - 3, 0, 9, 0, 0], [(1 << (8 * C.SB)) - 1] + [0] * (n - 1)):
+        want = C.msm([s % C.r for s in sc], pts)
+        for c, wpt, spt in ((3, 4, 1), (4, 1000, 2), (2, 7, 1), (5, 1000, 1)):   # several window groups / all windows in one slot
+            raw, inf = run(sc, n, c=c, wpt=wpt, spt=spt)
+            assert raw == C.g1_to_octet(want)[1:] and inf[0] == int(want is None), (sc[:2], c, wpt, spt)
+    # a point range and a batch of two
+    sc = [rng.randrange(C.r) for _ in range(6)]
+    raw, inf = run(sc, 3, batch=2, off=2, c=3, wpt=5)
+    for b in range(2):
+        want = C.msm(sc[3 * b:3 * b + 3], pts[2:5])
+        assert raw[b * 2 * C.M:(b + 1) * 2 * C.M] == C.g1_to_octet(want)[1:] and inf[b] == int(want is None), b
